@@ -1,0 +1,234 @@
+// Generation kernels: KV-cache append, single-position decode attention, fused softmax sampler.
+//
+// The reference re-runs the whole model over the whole context for every new token and samples
+// with softmax + torch.multinomial on fp32 logits (reference src/models/transformer.py:96-114).
+// Here each step touches one position: its K/V rows are appended to a [B, H, Tmax, hs] cache, the
+// query attends to the cache with an online softmax, and the next token is drawn from the
+// last-position logits by inverse-CDF sampling inside one kernel (no host sync per token).
+#include "b200llm.h"
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) kv_append_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ kc,
+                                                        bf16* __restrict__ vc, int B, int t, int H, int hs, int Tmax,
+                                                        int pos0, const int* __restrict__ pos_dev) {
+    if (pos_dev != nullptr) pos0 = *pos_dev;
+    const int cpr = hs / 8;  // 16-byte chunks per (row, head)
+    const long long total = (long long)B * t * H * cpr;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cpr);
+        const int h = (int)((i / cpr) % H);
+        const int tt = (int)((i / ((long long)cpr * H)) % t);
+        const int b = (int)(i / ((long long)cpr * H * t));
+        const size_t src = ((size_t)b * t + tt) * (3 * H * hs) + (size_t)H * hs + h * hs + c * 8;
+        const size_t dst = (((size_t)b * H + h) * Tmax + pos0 + tt) * hs + c * 8;
+        *reinterpret_cast<uint4*>(kc + dst) = *reinterpret_cast<const uint4*>(qkv + src);
+        *reinterpret_cast<uint4*>(vc + dst) = *reinterpret_cast<const uint4*>(qkv + src + (size_t)H * hs);
+    }
+}
+
+constexpr int DEC_WARPS = 8;
+
+template <int HD>
+__global__ void __launch_bounds__(DEC_WARPS * 32) attn_decode_kernel(const bf16* __restrict__ qkv,
+                                                                     const bf16* __restrict__ kc,
+                                                                     const bf16* __restrict__ vc, bf16* __restrict__ out,
+                                                                     int H, int Tmax, int len, float scale,
+                                                                     const int* __restrict__ pos_dev) {
+    if (pos_dev != nullptr) len = *pos_dev + 1;
+    constexpr int VPL = HD / 32;  // output columns per lane
+    __shared__ float s_q[HD];
+    __shared__ float s_m[DEC_WARPS], s_l[DEC_WARPS];
+    __shared__ float s_acc[DEC_WARPS][HD];
+    const int h = blockIdx.x, b = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x < HD)
+        s_q[threadIdx.x] = __bfloat162float(qkv[(size_t)b * 3 * H * HD + h * HD + threadIdx.x]) * scale;
+    __syncthreads();
+    const bf16* kb = kc + ((size_t)b * H + h) * Tmax * HD;
+    const bf16* vb = vc + ((size_t)b * H + h) * Tmax * HD;
+
+    float m = -INFINITY, l = 0.f, acc[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+
+    for (int j0 = warp * 32; j0 < len; j0 += DEC_WARPS * 32) {
+        // phase A: lane <-> key j0 + lane, full dot product
+        const int j = j0 + lane;
+        float s = -INFINITY;
+        if (j < len) {
+            const uint4* kr = reinterpret_cast<const uint4*>(kb + (size_t)j * HD);
+            float d = 0.f;
+#pragma unroll
+            for (int c = 0; c < HD / 8; ++c) {
+                const uint4 u = ldg_stream_u4(kr + c);
+                const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z),
+                             f3 = unpack_bf16x2(u.w);
+                d += f0.x * s_q[c * 8] + f0.y * s_q[c * 8 + 1] + f1.x * s_q[c * 8 + 2] + f1.y * s_q[c * 8 + 3] +
+                     f2.x * s_q[c * 8 + 4] + f2.y * s_q[c * 8 + 5] + f3.x * s_q[c * 8 + 6] + f3.y * s_q[c * 8 + 7];
+            }
+            s = d;
+        }
+        // phase B: online softmax over the 32 keys
+        const float mnew = fmaxf(m, warp_max(s));
+        const float corr = __expf(m - mnew);
+        const float p = j < len ? __expf(s - mnew) : 0.f;
+        l = l * corr + warp_sum(p);
+        m = mnew;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) acc[i] *= corr;
+        // phase C: acc += sum_j p_j V[j, lane cols]
+        const int nk = min(32, len - j0);
+#pragma unroll 8
+        for (int jj = 0; jj < nk; ++jj) {
+            const float pj = __shfl_sync(0xffffffffu, p, jj);
+            const bf16* vr = vb + (size_t)(j0 + jj) * HD + lane * VPL;
+            if (VPL == 2) {
+                const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(vr));
+                acc[0] += pj * f.x; acc[1] += pj * f.y;
+            } else {
+                const uint2 u = *reinterpret_cast<const uint2*>(vr);
+                const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
+                acc[0] += pj * f0.x; acc[1] += pj * f0.y; acc[2] += pj * f1.x; acc[3] += pj * f1.y;
+            }
+        }
+    }
+    if (lane == 0) { s_m[warp] = m; s_l[warp] = l; }
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) s_acc[warp][lane * VPL + i] = acc[i];
+    __syncthreads();
+    if (threadIdx.x < HD) {
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < DEC_WARPS; ++w) M = fmaxf(M, s_m[w]);
+        float L = 0.f, o = 0.f;
+#pragma unroll
+        for (int w = 0; w < DEC_WARPS; ++w) {
+            const float f = s_m[w] == -INFINITY ? 0.f : __expf(s_m[w] - M);
+            L += s_l[w] * f;
+            o += s_acc[w][threadIdx.x] * f;
+        }
+        out[(size_t)b * H * HD + h * HD + threadIdx.x] = __float2bfloat16_rn(L > 0.f ? o / L : 0.f);
+    }
+}
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
+constexpr int SAMP_THREADS = 1024;
+
+// One CTA per row: max -> sum exp -> inverse CDF at u * sum.
+__global__ void __launch_bounds__(SAMP_THREADS) sample_kernel(const bf16* __restrict__ logits, long long ld,
+                                                              long long* __restrict__ next, int V, float inv_temp,
+                                                              unsigned long long seed, unsigned long long step,
+                                                              const int* __restrict__ pos_dev) {
+    if (pos_dev != nullptr) step += (unsigned long long)*pos_dev;
+    __shared__ float s_red[32];
+    __shared__ int s_pick;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bf16* row = logits + (size_t)b * ld;
+    const int per = (V + SAMP_THREADS - 1) / SAMP_THREADS;
+    const int i0 = tid * per, i1 = min(V, i0 + per);
+    float mx = -INFINITY;
+    for (int i = i0; i < i1; ++i) mx = fmaxf(mx, __bfloat162float(row[i]) * inv_temp);
+    mx = warp_max(mx);
+    if (lane == 0) s_red[warp] = mx;
+    __syncthreads();
+    mx = s_red[lane];
+    mx = warp_max(mx);
+    __syncthreads();
+    float part = 0.f;
+    for (int i = i0; i < i1; ++i) part += __expf(__bfloat162float(row[i]) * inv_temp - mx);
+    // inclusive scan of per-thread partial sums
+    float v = part;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+    }
+    if (lane == 31) s_red[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        float w = s_red[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const float n = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += n;
+        }
+        s_red[lane] = w;
+    }
+    if (tid == 0) s_pick = -1;
+    __syncthreads();
+    const float incl = v + (warp > 0 ? s_red[warp - 1] : 0.f);
+    const float total = s_red[31];
+    const unsigned long long r = mix64(mix64(seed ^ (step * 0xD1B54A32D192ED03ull)) + (unsigned long long)b);
+    const float u = (float)((r >> 40) + 0.5) * (1.0f / 16777216.0f);  // (0,1)
+    const float target = u * total;
+    const float excl = incl - part;
+    if (target >= excl && target < incl && i0 < i1) {
+        float c = excl;
+        int pick = i1 - 1;
+        for (int i = i0; i < i1; ++i) {
+            c += __expf(__bfloat162float(row[i]) * inv_temp - mx);
+            if (target < c) { pick = i; break; }
+        }
+        atomicMax(&s_pick, pick);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int pick = s_pick;
+        if (pick < 0) {  // rounding fell off the end: take the last token with non-zero mass
+            pick = V - 1;
+        }
+        next[b] = pick;
+    }
+}
+
+}  // namespace
+
+extern "C" int b200_kv_append(const void* qkv, void* kcache, void* vcache, int B, int t, int H, int hs, int Tmax, int pos0,
+                              const int* pos_dev, cudaStream_t st) {
+    B200_REQUIRE(hs % 8 == 0 && pos0 >= 0 && pos0 + t <= Tmax, "kv_append: bad shape (hs=%d pos0=%d t=%d Tmax=%d)", hs,
+                 pos0, t, Tmax);
+    const long long total = (long long)B * t * H * (hs / 8);
+    long long nb = (total + 255) / 256;
+    const long long cap = (long long)b200_num_sms() * 8;
+    const int blocks = (int)(nb < cap ? nb : cap);
+    kv_append_kernel<<<max(blocks, 1), 256, 0, st>>>((const bf16*)qkv, (bf16*)kcache, (bf16*)vcache, B, t, H, hs, Tmax,
+                                                      pos0, pos_dev);
+    B200_RETURN_LAUNCH_STATUS("kv_append");
+}
+
+extern "C" int b200_attn_decode(const void* qkv, const void* kcache, const void* vcache, void* out, int B, int H, int hs,
+                                int Tmax, int len, float scale, const int* pos_dev, cudaStream_t st) {
+    B200_REQUIRE(hs == 64 || hs == 128, "attn_decode: head size must be 64 or 128");
+    B200_REQUIRE(len >= 1 && len <= Tmax, "attn_decode: bad len");
+    dim3 grid(H, B);
+    if (hs == 64)
+        attn_decode_kernel<64><<<grid, DEC_WARPS * 32, 0, st>>>((const bf16*)qkv, (const bf16*)kcache,
+                                                                (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev);
+    else
+        attn_decode_kernel<128><<<grid, DEC_WARPS * 32, 0, st>>>((const bf16*)qkv, (const bf16*)kcache,
+                                                                 (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev);
+    B200_RETURN_LAUNCH_STATUS("attn_decode");
+}
+
+extern "C" int b200_sample(const void* logits, long long ld, long long* next, int B, int V, float temperature, int top_k,
+                           unsigned long long seed, unsigned long long step, const int* pos_dev, cudaStream_t st) {
+    B200_REQUIRE(top_k <= 0, "sample: top_k filtering is applied by the caller (mask logits), pass top_k=0");
+    B200_REQUIRE(temperature > 0.f, "sample: temperature must be > 0");
+    sample_kernel<<<B, SAMP_THREADS, 0, st>>>((const bf16*)logits, ld, next, V, 1.f / temperature, seed, step, pos_dev);
+    B200_RETURN_LAUNCH_STATUS("sample");
+}
+
+__global__ void incr_kernel(int* p, int delta) { *p += delta; }
+extern "C" int b200_incr_int(int* p, int delta, cudaStream_t st) {
+    incr_kernel<<<1, 1, 0, st>>>(p, delta);
+    B200_RETURN_LAUNCH_STATUS("incr_int");
+}

@@ -1,0 +1,287 @@
+// Fused residual-add + LayerNorm, forward and backward.
+//
+// Forward replaces, per block of the reference, `x = x + branch` followed by `ln(x)`
+// (reference src/models/transformer_block.py:44,46; transformer.py:70): one pass reads the
+// fp32 residual stream and the bf16 branch output, writes the updated fp32 residual, the
+// bf16 normalised activations for the GEMM that follows, and the row statistics.
+// Backward fuses LN-backward with the residual-gradient accumulation, emits the bf16 copy of
+// the residual gradient that the next GEMMs consume, and produces per-CTA partial sums for
+// dgamma / dbeta (and, optionally, the column sums of the incoming residual gradient = the
+// bias gradient of the Linear that fed this residual).
+//
+// Thread mapping: a row is handled by WPR warps, each lane holding VPL float4 (d = 128*VPL*WPR)
+// in registers, so every element is read exactly once.  CTAs have 8 warps = 8/WPR row groups
+// that synchronise among themselves with named barriers only.
+#include "b200llm.h"
+#include "common.cuh"
+
+namespace {
+
+template <int WPR>
+__device__ __forceinline__ void group_bar(int group) {
+    if (WPR > 1) asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "r"(WPR * 32) : "memory");
+}
+
+template <int WPR>
+__device__ __forceinline__ float group_sum(float v, float* sred, int wir, int group, int lane) {
+    v = warp_sum(v);
+    if (WPR == 1) return v;
+    if (lane == 0) sred[wir] = v;
+    group_bar<WPR>(group);
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < WPR; ++i) t += sred[i];
+    group_bar<WPR>(group);
+    return t;
+}
+
+template <int VPL, int WPR>
+__global__ void __launch_bounds__(256) ln_fwd_kernel(float* __restrict__ x, const bf16* __restrict__ branch,
+                                                     const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, bf16* __restrict__ out,
+                                                     float* __restrict__ out_f32, float* __restrict__ mean_out,
+                                                     float* __restrict__ rstd_out, int M, float eps) {
+    constexpr int G = 8 / WPR;
+    constexpr int D4 = 32 * WPR * VPL;  // float4 per row
+    __shared__ float sred_all[8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int group = warp / WPR, wir = warp % WPR;
+    float* sred = sred_all + group * WPR;
+    const int row = blockIdx.x * G + group;
+    if (row >= M) return;  // whole group exits together
+
+    float4 v[VPL];
+    float4* xr = reinterpret_cast<float4*>(x + (size_t)row * D4 * 4);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) v[i] = xr[wir * 32 + lane + i * 32 * WPR];
+    if (branch != nullptr) {
+        const uint2* br = reinterpret_cast<const uint2*>(branch + (size_t)row * D4 * 4);
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            uint2 u = ldg_stream_u2(br + wir * 32 + lane + i * 32 * WPR);
+            float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
+            v[i].x += a.x; v[i].y += a.y; v[i].z += b.x; v[i].w += b.y;
+            xr[wir * 32 + lane + i * 32 * WPR] = v[i];
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    const float mean = group_sum<WPR>(s, sred, wir, group, lane) * (1.f / (D4 * 4));
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, e = v[i].w - mean;
+        q += (a * a + b * b) + (c * c + e * e);
+    }
+    const float var = group_sum<WPR>(q, sred, wir, group, lane) * (1.f / (D4 * 4));
+    const float rstd = rsqrtf(var + eps);
+    if (wir == 0 && lane == 0) {
+        if (mean_out) mean_out[row] = mean;
+        if (rstd_out) rstd_out[row] = rstd;
+    }
+    const float4* g4 = reinterpret_cast<const float4*>(gamma);
+    const float4* b4 = reinterpret_cast<const float4*>(beta);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = wir * 32 + lane + i * 32 * WPR;
+        float4 g = __ldg(g4 + c), b = __ldg(b4 + c);
+        float4 y;
+        y.x = (v[i].x - mean) * rstd * g.x + b.x;
+        y.y = (v[i].y - mean) * rstd * g.y + b.y;
+        y.z = (v[i].z - mean) * rstd * g.z + b.z;
+        y.w = (v[i].w - mean) * rstd * g.w + b.w;
+        if (out) reinterpret_cast<uint2*>(out + (size_t)row * D4 * 4)[c] =
+                make_uint2(pack_bf16x2(y.x, y.y), pack_bf16x2(y.z, y.w));
+        if (out_f32) reinterpret_cast<float4*>(out_f32 + (size_t)row * D4 * 4)[c] = y;
+    }
+}
+
+template <int VPL, int WPR, bool COLSUM>
+__global__ void __launch_bounds__(256, 2)
+    ln_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean,
+                  const float* __restrict__ rstd, const float* __restrict__ gamma, const float* dx_in,
+                  float* dx_out, bf16* __restrict__ dx_bf16, float* __restrict__ partial, int M) {
+    constexpr int G = 8 / WPR;
+    constexpr int D4 = 32 * WPR * VPL;
+    constexpr int NACC = COLSUM ? 3 : 2;
+    __shared__ float sred_all[16];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int group = warp / WPR, wir = warp % WPR;
+    float* sred = sred_all + group * WPR * 2;
+
+    float4 acc_g[VPL], acc_b[VPL], acc_c[COLSUM ? VPL : 1];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        acc_g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        acc_b[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (COLSUM) acc_c[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const float4* g4 = reinterpret_cast<const float4*>(gamma);
+
+    for (int row = blockIdx.x * G + group; row < M; row += gridDim.x * G) {
+        const size_t base4 = (size_t)row * D4;
+        const float mu = mean[row], rs = rstd[row];
+        float4 xh[VPL], gd[VPL];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = wir * 32 + lane + i * 32 * WPR;
+            float4 xv = ldg_stream_f4(reinterpret_cast<const float4*>(x) + base4 + c);
+            uint2 u = ldg_stream_u2(reinterpret_cast<const uint2*>(dy) + base4 + c);
+            float2 d0 = unpack_bf16x2(u.x), d1 = unpack_bf16x2(u.y);
+            float4 g = __ldg(g4 + c);
+            xh[i].x = (xv.x - mu) * rs; xh[i].y = (xv.y - mu) * rs;
+            xh[i].z = (xv.z - mu) * rs; xh[i].w = (xv.w - mu) * rs;
+            acc_g[i].x += d0.x * xh[i].x; acc_g[i].y += d0.y * xh[i].y;
+            acc_g[i].z += d1.x * xh[i].z; acc_g[i].w += d1.y * xh[i].w;
+            acc_b[i].x += d0.x; acc_b[i].y += d0.y; acc_b[i].z += d1.x; acc_b[i].w += d1.y;
+            gd[i].x = d0.x * g.x; gd[i].y = d0.y * g.y; gd[i].z = d1.x * g.z; gd[i].w = d1.y * g.w;
+            s1 += (gd[i].x + gd[i].y) + (gd[i].z + gd[i].w);
+            s2 += (gd[i].x * xh[i].x + gd[i].y * xh[i].y) + (gd[i].z * xh[i].z + gd[i].w * xh[i].w);
+        }
+        s1 = warp_sum(s1);
+        s2 = warp_sum(s2);
+        if (WPR > 1) {
+            if (lane == 0) { sred[wir * 2] = s1; sred[wir * 2 + 1] = s2; }
+            group_bar<WPR>(group);
+            s1 = 0.f; s2 = 0.f;
+#pragma unroll
+            for (int i = 0; i < WPR; ++i) { s1 += sred[i * 2]; s2 += sred[i * 2 + 1]; }
+            group_bar<WPR>(group);
+        }
+        const float c1 = s1 * (1.f / (D4 * 4)), c2 = s2 * (1.f / (D4 * 4));
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+            const int c = wir * 32 + lane + i * 32 * WPR;
+            float4 r;
+            r.x = rs * (gd[i].x - c1 - xh[i].x * c2);
+            r.y = rs * (gd[i].y - c1 - xh[i].y * c2);
+            r.z = rs * (gd[i].z - c1 - xh[i].z * c2);
+            r.w = rs * (gd[i].w - c1 - xh[i].w * c2);
+            if (dx_in != nullptr) {
+                float4 p = reinterpret_cast<const float4*>(dx_in)[base4 + c];  // may alias dx_out
+                if (COLSUM) { acc_c[i].x += p.x; acc_c[i].y += p.y; acc_c[i].z += p.z; acc_c[i].w += p.w; }
+                r.x += p.x; r.y += p.y; r.z += p.z; r.w += p.w;
+            }
+            reinterpret_cast<float4*>(dx_out)[base4 + c] = r;
+            if (dx_bf16 != nullptr)
+                reinterpret_cast<uint2*>(dx_bf16)[base4 + c] =
+                    make_uint2(pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
+        }
+    }
+    // partial[(cta*G + group)][NACC][d]
+    float4* pr = reinterpret_cast<float4*>(partial) + (size_t)(blockIdx.x * G + group) * NACC * D4;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const int c = wir * 32 + lane + i * 32 * WPR;
+        pr[c] = acc_g[i];
+        pr[D4 + c] = acc_b[i];
+        if (COLSUM) pr[2 * D4 + c] = acc_c[i];
+    }
+}
+
+// out[k][c] (+)= sum_p partial[p][k][c]
+__global__ void __launch_bounds__(128) ln_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int nacc,
+                                                              int d, float* __restrict__ o0, float* __restrict__ o1,
+                                                              float* __restrict__ o2, int accumulate) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int k = blockIdx.y;
+    if (c >= d) return;
+    float* o = k == 0 ? o0 : (k == 1 ? o1 : o2);
+    if (o == nullptr) return;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    const float* p = partial + (size_t)k * d + c;
+    const size_t stride = (size_t)nacc * d;
+    int i = 0;
+    for (; i + 3 < nparts; i += 4) {
+        s0 += p[(size_t)i * stride];
+        s1 += p[(size_t)(i + 1) * stride];
+        s2 += p[(size_t)(i + 2) * stride];
+        s3 += p[(size_t)(i + 3) * stride];
+    }
+    for (; i < nparts; ++i) s0 += p[(size_t)i * stride];
+    float s = (s0 + s1) + (s2 + s3);
+    o[c] = accumulate ? o[c] + s : s;
+}
+
+struct LnCfg { int vpl, wpr; };
+inline bool ln_cfg(int d, LnCfg* c) {
+    switch (d) {
+        case 128: *c = {1, 1}; return true;
+        case 256: *c = {2, 1}; return true;
+        case 384: *c = {3, 1}; return true;
+        case 512: *c = {4, 1}; return true;
+        case 768: *c = {3, 2}; return true;
+        case 1024: *c = {4, 2}; return true;
+        case 1536: *c = {3, 4}; return true;
+        case 2048: *c = {4, 4}; return true;
+        case 3072: *c = {3, 8}; return true;
+        case 4096: *c = {4, 8}; return true;
+        default: return false;
+    }
+}
+
+}  // namespace
+
+#define LN_DISPATCH(VPL_, WPR_, ...)                    \
+    if (cfg.vpl == VPL_ && cfg.wpr == WPR_) {           \
+        constexpr int VPL = VPL_, WPR = WPR_;           \
+        __VA_ARGS__;                                    \
+    }
+#define LN_DISPATCH_ALL(...)                                                                         \
+    LN_DISPATCH(1, 1, __VA_ARGS__) LN_DISPATCH(2, 1, __VA_ARGS__) LN_DISPATCH(3, 1, __VA_ARGS__)     \
+    LN_DISPATCH(4, 1, __VA_ARGS__) LN_DISPATCH(3, 2, __VA_ARGS__) LN_DISPATCH(4, 2, __VA_ARGS__)     \
+    LN_DISPATCH(3, 4, __VA_ARGS__) LN_DISPATCH(4, 4, __VA_ARGS__) LN_DISPATCH(3, 8, __VA_ARGS__)     \
+    LN_DISPATCH(4, 8, __VA_ARGS__)
+
+extern "C" int b200_ln_supported(int d) {
+    LnCfg c;
+    return ln_cfg(d, &c) ? 1 : 0;
+}
+
+extern "C" int b200_ln_fwd(float* x, const void* branch, const float* gamma, const float* beta, void* out_bf16,
+                           float* out_f32, float* mean, float* rstd, int M, int d, float eps, cudaStream_t st) {
+    LnCfg cfg;
+    B200_REQUIRE(ln_cfg(d, &cfg), "ln_fwd: unsupported width d=%d", d);
+    if (M <= 0) return 0;
+    const int G = 8 / cfg.wpr;
+    const int grid = (M + G - 1) / G;
+    LN_DISPATCH_ALL((ln_fwd_kernel<VPL, WPR><<<grid, 256, 0, st>>>(x, (const bf16*)branch, gamma, beta,
+                                                                   (bf16*)out_bf16, out_f32, mean, rstd, M, eps)))
+    B200_RETURN_LAUNCH_STATUS("ln_fwd");
+}
+
+// number of partial rows ln_bwd writes for (M, d): the caller sizes `partial` as
+// nparts * (colsum ? 3 : 2) * d floats.
+extern "C" int b200_ln_bwd_nparts(int M, int d) {
+    LnCfg cfg;
+    if (!ln_cfg(d, &cfg)) return -1;
+    const int G = 8 / cfg.wpr;
+    int grid = min((M + G - 1) / G, b200_num_sms() * 2);
+    return max(grid, 1) * G;
+}
+
+extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* rstd,
+                           const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16,
+                           float* partial, float* dgamma, float* dbeta, float* colsum, int M, int d,
+                           int accumulate, cudaStream_t st) {
+    LnCfg cfg;
+    B200_REQUIRE(ln_cfg(d, &cfg), "ln_bwd: unsupported width d=%d", d);
+    if (M <= 0) return 0;
+    const int G = 8 / cfg.wpr;
+    const int grid = max(1, min((M + G - 1) / G, b200_num_sms() * 2));
+    const bool cs = colsum != nullptr;
+    B200_REQUIRE(!cs || dx_in != nullptr, "ln_bwd: colsum needs dx_in");
+    if (cs) {
+        LN_DISPATCH_ALL((ln_bwd_kernel<VPL, WPR, true><<<grid, 256, 0, st>>>(
+            (const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M)))
+    } else {
+        LN_DISPATCH_ALL((ln_bwd_kernel<VPL, WPR, false><<<grid, 256, 0, st>>>(
+            (const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M)))
+    }
+    const int nacc = cs ? 3 : 2;
+    ln_bwd_finalize_kernel<<<dim3((d + 127) / 128, nacc), 128, 0, st>>>(partial, grid * G, nacc, d, dgamma, dbeta,
+                                                                         colsum, accumulate);
+    B200_RETURN_LAUNCH_STATUS("ln_bwd");
+}

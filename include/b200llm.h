@@ -1,0 +1,100 @@
+/* libb200llm - C ABI of the hand-written sm_100a kernels.
+ *
+ * Conventions: every function returns 0 on success, non-zero on error (message via
+ * b200_last_error()); pointers are device pointers unless named h_*; `st` is the CUDA stream the
+ * work is enqueued on; nothing synchronises the device and - unless a function says otherwise -
+ * nothing allocates device memory, so the calls are capturable in CUDA graphs after a first
+ * eager call (which sets function attributes and fills the TMA-descriptor cache).
+ * bf16 tensors are passed as void*.  Matrices are row-major with an explicit leading dimension
+ * in elements.  Citations "ref:" point at the reference code each entry point replaces.
+ *
+ * The Python side parses THIS FILE to build its ctypes signatures (ops/lib.py): keep one
+ * declaration per statement, plain C types only.
+ */
+#ifndef B200LLM_H
+#define B200LLM_H
+
+#include <cuda_runtime.h>
+
+#define B200_ABI_VERSION 1
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* b200_last_error(void);
+int b200_abi_version(void);
+
+/* ---- utility ------------------------------------------------------------------------------ */
+int b200_cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t st);
+/* out[N] (+)= column sums of bf16 a[M,N] (bias gradients; ref: autograd of nn.Linear bias, mlp.py:24-26) */
+int b200_colsum_bf16(const void* a, float* out, int M, int N, int ld, int accumulate, cudaStream_t st);
+int b200_l2_flush(void* buf, long long bytes, cudaStream_t st);
+
+/* ---- embedding (ref: src/models/transformer.py:51-54) -------------------------------------- */
+/* x[b*T+t, :] = wte[idx[b,t], :] + wpe[pos0 + t, :]   (fp32) */
+int b200_embed_fwd(const long long* idx, const float* wte, const float* wpe, float* x, int B, int T, int d, int V, int pos0, const int* pos_dev, cudaStream_t st);
+/* dwte[idx[m], :] += dx[m, :] (vector RED; caller zeroes dwte on the first micro-step);
+ * dwpe[t, :] (+)= sum_b dx[b, t, :] */
+int b200_embed_bwd(const long long* idx, const float* dx, float* dwte, float* dwpe, int B, int T, int d, int V, int accumulate, cudaStream_t st);
+
+/* ---- fused residual-add + LayerNorm (ref: src/models/transformer_block.py:44,46; transformer.py:70) */
+int b200_ln_supported(int d);
+/* if branch: x += branch (fp32 residual updated in place); out = LN(x) * gamma + beta.
+ * out_bf16 / out_f32 / mean / rstd may each be null. */
+int b200_ln_fwd(float* x, const void* branch, const float* gamma, const float* beta, void* out_bf16, float* out_f32, float* mean, float* rstd, int M, int d, float eps, cudaStream_t st);
+int b200_ln_bwd_nparts(int M, int d);
+/* dx_out = (dx_in or 0) + LN-backward(dy); dx_bf16 = bf16(dx_out) (nullable); dgamma/dbeta (+)=;
+ * colsum (nullable) (+)= column sums of dx_in.  `partial` is scratch of
+ * b200_ln_bwd_nparts(M,d) * (colsum ? 3 : 2) * d floats.  dx_in may alias dx_out. */
+int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16, float* partial, float* dgamma, float* dbeta, float* colsum, int M, int d, int accumulate, cudaStream_t st);
+
+/* ---- tcgen05 GEMM (ref: every nn.Linear fwd/bwd: attention.py:47-55, mlp.py:53,66, transformer.py:71)
+ * C[M,N] = alpha * opA * opB^T.   a_mn = 0: A is [M,K] (K contiguous); 1: A is [K,M].
+ *                                  b_mn = 0: B is [N,K] (K contiguous); 1: B is [K,N].
+ * out_f32 = 0: C bf16 via TMA store, epilogue = (+bias[N]) (ReLU) (* (mask[M,N] > 0)), and if
+ *              `stats` != null per-(n-tile,row) float2 (max, sum exp) -> stats[n_tile * M + row]
+ *              with n-tile width b200_gemm_pick_bn() or bn_override.
+ * out_f32 = 1: C fp32, f32_mode 0 store / 1 accumulate / 2 atomic add (enables split-K;
+ *              split_k = 0 picks automatically, C must then hold the running sum). */
+int b200_gemm_pick_bn(int M, int N, int K, int out_f32);
+int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn_override, int split_k, cudaStream_t st);
+
+/* ---- fused AdamW (ref: scripts/train_transformer.py:92,126 torch.optim.AdamW defaults) -------
+ * hyper (device, 8 floats) = lr, beta1, beta2, eps, weight_decay, bias_correction1,
+ * sqrt(bias_correction2), grad_scale.  p_bf16 (nullable) receives the bf16 shadow weights. */
+int b200_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, const float* hyper, long long n, cudaStream_t st);
+
+/* ---- softmax cross-entropy on bf16 logits (ref: src/models/transformer.py:74-77) ------------
+ * finalize: combines the GEMM-epilogue statistics stats[n_tiles][M] into lse[M], reads the
+ * target logit, writes loss_rows[M] = lse - logit[target] and loss_sum[0] (+)= sum of rows. */
+int b200_ce_finalize(const void* stats, int n_tiles, const void* logits, long long ld, const long long* targets, float* lse, float* loss_rows, float* loss_sum, int M, int V, cudaStream_t st);
+/* in place: logits[m, v] = (exp(logits - lse[m]) - [v == target[m]]) * scale  (bf16), and
+ * dbias[V] (+)= column sums of the result (ref: lm_head bias gradient) */
+int b200_ce_grad(void* logits, long long ld, const float* lse, const long long* targets, float* dbias, int M, int V, float scale, int accumulate, cudaStream_t st);
+
+/* ---- causal flash attention on packed qkv (ref: src/models/attention.py:45-58,95) -----------
+ * qkv [B*T, 3*H*hs] bf16 (q | k | v thirds, head h at columns h*hs); out [B*T, H*hs] bf16
+ * head-major (the reference's torch.cat of heads); lse [B, H, T] fp32. hs in {64, 128}. */
+int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale, cudaStream_t st);
+/* dqkv [B*T, 3*H*hs] bf16; delta [B, H, T] fp32 scratch; dq_acc [B*T, H*hs] fp32 scratch */
+int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t st);
+
+/* ---- generation (ref: src/models/transformer.py:96-114) ------------------------------------
+ * pos_dev (nullable, device int): when given it overrides pos0 / len (= *pos_dev + 1) / adds to the
+ * sampler step, so that one captured CUDA graph can be replayed for every decode position.
+ * KV cache layout [B, H, Tmax, hs] bf16 for k and v.  append: copies the k/v thirds of
+ * qkv [B*t, 3*H*hs] into the caches at positions pos0..pos0+t-1. */
+int b200_kv_append(const void* qkv, void* kcache, void* vcache, int B, int t, int H, int hs, int Tmax, int pos0, const int* pos_dev, cudaStream_t st);
+/* single-position decode attention: q = q-third of qkv [B, 3*H*hs], attends to cache[0..len) */
+int b200_attn_decode(const void* qkv, const void* kcache, const void* vcache, void* out, int B, int H, int hs, int Tmax, int len, float scale, const int* pos_dev, cudaStream_t st);
+/* next[b] ~ softmax(logits[b, :] / temperature) restricted to the top_k largest (top_k <= 0: all);
+ * Philox-free counter RNG: (seed, step, b) -> uniform.  logits bf16 [B, ld]. */
+int b200_sample(const void* logits, long long ld, long long* next, int B, int V, float temperature, int top_k, unsigned long long seed, unsigned long long step, const int* pos_dev, cudaStream_t st);
+
+int b200_incr_int(int* p, int delta, cudaStream_t st);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,206 @@
+"""Python face of the native kernels: thin, allocation-light wrappers around the C ABI.
+
+Every wrapper enqueues on ``torch.cuda.current_stream()``, does no host synchronisation and
+raises if the native library reports an error.  Output buffers may be passed in (the engine
+preallocates everything so a training step is CUDA-graph capturable); when omitted they are
+allocated with torch.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+
+from . import lib
+
+BF16 = torch.bfloat16
+F32 = torch.float32
+
+
+def _st() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _chk(rc: int, what: str) -> None:
+    if rc != 0:
+        lib.check(rc, what)
+
+
+# ------------------------------------------------------------------------------------------ GEMM
+def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *, a_mn: bool = False,
+         b_mn: bool = False, out_dtype=BF16, f32_mode: int = 0, alpha: float = 1.0,
+         bias: Optional[torch.Tensor] = None, relu: bool = False, mask: Optional[torch.Tensor] = None,
+         stats: Optional[torch.Tensor] = None, bn: int = 0, split_k: int = 0) -> torch.Tensor:
+    """C[M,N] = alpha * opA @ opB^T on the tcgen05 kernel.
+
+    a: [M,K] (a_mn=False) or [K,M] (a_mn=True); b: [N,K] (b_mn=False) or [K,N] (b_mn=True); bf16,
+    last dim contiguous.  out bf16 (epilogue: +bias, ReLU, *(mask>0), softmax stats) or fp32
+    (f32_mode 0 store / 1 accumulate / 2 atomic+split-K)."""
+    assert a.dtype == BF16 and b.dtype == BF16 and a.stride(-1) == 1 and b.stride(-1) == 1
+    if a_mn:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb, f"inner dimensions differ: {K} vs {Kb}"
+    if out is None:
+        out = torch.empty(M, N, device=a.device, dtype=out_dtype)
+        if out_dtype == F32 and f32_mode != 0:
+            out.zero_()
+    assert out.shape == (M, N) and out.stride(-1) == 1
+    out_f32 = out.dtype == F32
+    assert out_f32 or out.dtype == BF16
+    L = lib.load()
+    rc = L.b200_gemm(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
+                     int(a_mn), int(b_mn), int(out_f32), f32_mode, float(alpha), _p(bias), int(relu),
+                     _p(mask), 0 if mask is None else mask.stride(0), _p(stats), bn, split_k, _st())
+    _chk(rc, "gemm")
+    return out
+
+
+def gemm_pick_bn(M: int, N: int, K: int, out_f32: bool = False) -> int:
+    return lib.load().b200_gemm_pick_bn(M, N, K, int(out_f32))
+
+
+# ------------------------------------------------------------------------------------------ elementwise
+def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    assert x.dtype == F32 and x.is_contiguous()
+    if out is None:
+        out = torch.empty_like(x, dtype=BF16)
+    _chk(lib.load().b200_cast_f32_bf16(_p(x), _p(out), x.numel(), _st()), "cast")
+    return out
+
+
+def colsum(a: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+    M, N = a.shape
+    if out is None:
+        out = torch.zeros(N, device=a.device, dtype=F32)
+    _chk(lib.load().b200_colsum_bf16(_p(a), _p(out), M, N, a.stride(0), int(accumulate), _st()), "colsum")
+    return out
+
+
+def embed_fwd(idx, wte, wpe, out=None, pos0: int = 0, pos_dev=None):
+    B, T = idx.shape
+    V, d = wte.shape
+    assert idx.dtype == torch.int64 and idx.is_contiguous()
+    if out is None:
+        out = torch.empty(B * T, d, device=wte.device, dtype=F32)
+    _chk(lib.load().b200_embed_fwd(_p(idx), _p(wte), _p(wpe), _p(out), B, T, d, V, pos0, _p(pos_dev), _st()),
+         "embed_fwd")
+    return out
+
+
+def embed_bwd(idx, dx, dwte, dwpe, accumulate: bool = False):
+    B, T = idx.shape
+    V, d = dwte.shape
+    _chk(lib.load().b200_embed_bwd(_p(idx), _p(dx), _p(dwte), _p(dwpe), B, T, d, V, int(accumulate), _st()),
+         "embed_bwd")
+
+
+def ln_fwd(x, gamma, beta, *, branch=None, out=None, out_f32=None, mean=None, rstd=None, eps: float = 1e-5,
+           want_stats: bool = True):
+    """x (fp32 [M,d], updated in place when branch is given) -> bf16 LN output (+ mean, rstd)."""
+    M, d = x.shape
+    if out is None and out_f32 is None:
+        out = torch.empty(M, d, device=x.device, dtype=BF16)
+    if want_stats and mean is None:
+        mean = torch.empty(M, device=x.device, dtype=F32)
+        rstd = torch.empty(M, device=x.device, dtype=F32)
+    _chk(lib.load().b200_ln_fwd(_p(x), _p(branch), _p(gamma), _p(beta), _p(out), _p(out_f32), _p(mean), _p(rstd),
+                                M, d, eps, _st()), "ln_fwd")
+    return out if out is not None else out_f32, mean, rstd
+
+
+def ln_bwd_nparts(M: int, d: int) -> int:
+    return lib.load().b200_ln_bwd_nparts(M, d)
+
+
+def ln_bwd(dy, x, mean, rstd, gamma, dgamma, dbeta, *, dx_in=None, dx_out=None, dx_bf16=None, colsum_out=None,
+           partial=None, accumulate: bool = False):
+    M, d = x.shape
+    if dx_out is None:
+        dx_out = torch.empty(M, d, device=x.device, dtype=F32)
+    if partial is None:
+        partial = torch.empty(ln_bwd_nparts(M, d) * 3 * d, device=x.device, dtype=F32)
+    _chk(lib.load().b200_ln_bwd(_p(dy), _p(x), _p(mean), _p(rstd), _p(gamma), _p(dx_in), _p(dx_out), _p(dx_bf16),
+                                _p(partial), _p(dgamma), _p(dbeta), _p(colsum_out), M, d, int(accumulate), _st()),
+         "ln_bwd")
+    return dx_out
+
+
+def adamw(p, g, m, v, p_bf16, hyper):
+    _chk(lib.load().b200_adamw(_p(p), _p(g), _p(m), _p(v), _p(p_bf16), _p(hyper), p.numel(), _st()), "adamw")
+
+
+def adamw_hyper(lr: float, step: int, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01, grad_scale=1.0):
+    """The 8 floats b200_adamw reads (same derivations as torch.optim.AdamW's single step)."""
+    bc1 = 1.0 - beta1 ** step
+    bc2 = 1.0 - beta2 ** step
+    return [lr, beta1, beta2, eps, weight_decay, bc1, math.sqrt(bc2), grad_scale]
+
+
+# ------------------------------------------------------------------------------------------ CE
+def ce_finalize(stats, n_tiles, logits, targets, lse, loss_rows, loss_sum, V):
+    M = logits.shape[0]
+    _chk(lib.load().b200_ce_finalize(_p(stats), n_tiles, _p(logits), logits.stride(0), _p(targets), _p(lse),
+                                     _p(loss_rows), _p(loss_sum), M, V, _st()), "ce_finalize")
+
+
+def ce_grad(logits, lse, targets, dbias, V, scale: float, accumulate: bool = False):
+    M = logits.shape[0]
+    _chk(lib.load().b200_ce_grad(_p(logits), logits.stride(0), _p(lse), _p(targets), _p(dbias), M, V, scale,
+                                 int(accumulate), _st()), "ce_grad")
+
+
+# ------------------------------------------------------------------------------------------ attention
+def attn_fwd(qkv, B, T, H, hs, out=None, lse=None):
+    if out is None:
+        out = torch.empty(B * T, H * hs, device=qkv.device, dtype=BF16)
+    if lse is None:
+        lse = torch.empty(B, H, T, device=qkv.device, dtype=F32)
+    _chk(lib.load().b200_attn_fwd(_p(qkv), _p(out), _p(lse), B, T, H, hs, 1.0 / math.sqrt(hs), _st()), "attn_fwd")
+    return out, lse
+
+
+def attn_bwd(qkv, out, dout, lse, B, T, H, hs, dqkv=None, delta=None, dq_acc=None):
+    if dqkv is None:
+        dqkv = torch.empty_like(qkv)
+    if delta is None:
+        delta = torch.empty(B, H, T, device=qkv.device, dtype=F32)
+    if dq_acc is None:
+        dq_acc = torch.zeros(B * T, H * hs, device=qkv.device, dtype=F32)
+    _chk(lib.load().b200_attn_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_acc), _p(dqkv), B, T, H, hs,
+                                  1.0 / math.sqrt(hs), _st()), "attn_bwd")
+    return dqkv
+
+
+def kv_append(qkv, kcache, vcache, B, t, H, hs, Tmax, pos0=0, pos_dev=None):
+    _chk(lib.load().b200_kv_append(_p(qkv), _p(kcache), _p(vcache), B, t, H, hs, Tmax, pos0, _p(pos_dev), _st()),
+         "kv_append")
+
+
+def attn_decode(qkv, kcache, vcache, out, B, H, hs, Tmax, length=1, pos_dev=None):
+    _chk(lib.load().b200_attn_decode(_p(qkv), _p(kcache), _p(vcache), _p(out), B, H, hs, Tmax, length,
+                                     1.0 / math.sqrt(hs), _p(pos_dev), _st()), "attn_decode")
+
+
+def sample(logits, next_tok, V, temperature=1.0, seed=0, step=0, pos_dev=None):
+    B = logits.shape[0]
+    _chk(lib.load().b200_sample(_p(logits), logits.stride(0), _p(next_tok), B, V, float(temperature), 0, seed, step,
+                                _p(pos_dev), _st()), "sample")
+
+
+def incr_int(t: torch.Tensor, delta: int = 1):
+    _chk(lib.load().b200_incr_int(_p(t), delta, _st()), "incr_int")
+
+
+def l2_flush(buf: torch.Tensor):
+    _chk(lib.load().b200_l2_flush(_p(buf), buf.numel() * buf.element_size(), _st()), "l2_flush")
