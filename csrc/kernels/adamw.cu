@@ -5,27 +5,29 @@
 // operation order (decoupled weight decay on every parameter, lerp for exp_avg, bias
 // corrections applied as step_size = lr/bc1 and denom = sqrt(v)/sqrt(bc2) + eps) so that it
 // tracks torch.optim.AdamW to rounding.  Hyper-parameters come from an 8-float device array so
-// a captured CUDA graph picks up the new learning rate / bias corrections on every replay:
-//   hyper = { lr, beta1, beta2, eps, weight_decay, bias_correction1, sqrt(bias_correction2), grad_scale }
+// a captured CUDA graph picks up the new learning rate / bias corrections on every replay.  The
+// derived scalars are computed on the host in double and rounded once, like torch does:
+//   hyper = { 1 - lr*wd, beta2, 1 - beta1, 1 - beta2, lr / bias_correction1, sqrt(bias_correction2),
+//             eps, grad_scale }
 #include "b200llm.h"
 #include "common.cuh"
 
-__device__ __forceinline__ void adamw_elem(float& p, float g, float& m, float& v, float lr, float b1, float b2,
-                                           float eps, float wd, float bc1, float bc2s, float gs) {
+__device__ __forceinline__ void adamw_elem(float& p, float g, float& m, float& v, float decay, float b2, float w1,
+                                           float w2, float step_size, float bc2s, float eps, float gs) {
     g *= gs;
-    p = p * (1.f - lr * wd);
-    m = m + (g - m) * (1.f - b1);
-    v = v * b2 + (1.f - b2) * g * g;
+    p = p * decay;                         // param.mul_(1 - lr * weight_decay)
+    m = fmaf(w1, g - m, m);                // exp_avg.lerp_(grad, 1 - beta1)
+    v = fmaf(w2 * g, g, v * b2);           // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
     const float denom = __fdiv_rn(__fsqrt_rn(v), bc2s) + eps;
-    p = p - __fdiv_rn(lr, bc1) * __fdiv_rn(m, denom);
+    p = fmaf(-step_size, __fdiv_rn(m, denom), p);   // param.addcdiv_(exp_avg, denom, value=-step_size)
 }
 
 __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                     float* __restrict__ m, float* __restrict__ v,
                                                     bf16* __restrict__ pb, const float* __restrict__ hyper,
                                                     long long n) {
-    const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], bc1 = hyper[5],
-                bc2s = hyper[6], gs = hyper[7];
+    const float decay = hyper[0], b2 = hyper[1], w1 = hyper[2], w2 = hyper[3], step_size = hyper[4],
+                bc2s = hyper[5], eps = hyper[6], gs = hyper[7];
     const long long n4 = n >> 2;
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -34,10 +36,10 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const
         float4 gv = ldg_stream_f4(reinterpret_cast<const float4*>(g) + i);
         float4 mv = reinterpret_cast<float4*>(m)[i];
         float4 vv = reinterpret_cast<float4*>(v)[i];
-        adamw_elem(pv.x, gv.x, mv.x, vv.x, lr, b1, b2, eps, wd, bc1, bc2s, gs);
-        adamw_elem(pv.y, gv.y, mv.y, vv.y, lr, b1, b2, eps, wd, bc1, bc2s, gs);
-        adamw_elem(pv.z, gv.z, mv.z, vv.z, lr, b1, b2, eps, wd, bc1, bc2s, gs);
-        adamw_elem(pv.w, gv.w, mv.w, vv.w, lr, b1, b2, eps, wd, bc1, bc2s, gs);
+        adamw_elem(pv.x, gv.x, mv.x, vv.x, decay, b2, w1, w2, step_size, bc2s, eps, gs);
+        adamw_elem(pv.y, gv.y, mv.y, vv.y, decay, b2, w1, w2, step_size, bc2s, eps, gs);
+        adamw_elem(pv.z, gv.z, mv.z, vv.z, decay, b2, w1, w2, step_size, bc2s, eps, gs);
+        adamw_elem(pv.w, gv.w, mv.w, vv.w, decay, b2, w1, w2, step_size, bc2s, eps, gs);
         reinterpret_cast<float4*>(p)[i] = pv;
         reinterpret_cast<float4*>(m)[i] = mv;
         reinterpret_cast<float4*>(v)[i] = vv;
@@ -47,7 +49,7 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         for (long long j = n4 << 2; j < n; ++j) {
             float pj = p[j], mj = m[j], vj = v[j];
-            adamw_elem(pj, g[j], mj, vj, lr, b1, b2, eps, wd, bc1, bc2s, gs);
+            adamw_elem(pj, g[j], mj, vj, decay, b2, w1, w2, step_size, bc2s, eps, gs);
             p[j] = pj; m[j] = mj; v[j] = vj;
             if (pb != nullptr) pb[j] = __float2bfloat16_rn(pj);
         }

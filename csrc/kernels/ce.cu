@@ -12,7 +12,7 @@ __global__ void __launch_bounds__(256) ce_finalize_kernel(const float2* __restri
                                                           const bf16* __restrict__ logits, long long ld,
                                                           const long long* __restrict__ targets,
                                                           float* __restrict__ lse, float* __restrict__ loss_rows,
-                                                          float* __restrict__ loss_sum, int M, int V) {
+                                                          float* __restrict__ loss_sum, int M, int V, float sum_scale) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x;
     float loss = 0.f;
     if (m < M) {
@@ -39,15 +39,15 @@ __global__ void __launch_bounds__(256) ce_finalize_kernel(const float2* __restri
         v += __shfl_xor_sync(0xffu, v, 4);
         v += __shfl_xor_sync(0xffu, v, 2);
         v += __shfl_xor_sync(0xffu, v, 1);
-        if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, v);
+        if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, v * sum_scale);
     }
 }
 
 extern "C" int b200_ce_finalize(const void* stats, int n_tiles, const void* logits, long long ld,
                                 const long long* targets, float* lse, float* loss_rows, float* loss_sum, int M, int V,
-                                cudaStream_t st) {
+                                float sum_scale, cudaStream_t st) {
     ce_finalize_kernel<<<(M + 255) / 256, 256, 0, st>>>((const float2*)stats, n_tiles, (const bf16*)logits, ld, targets,
-                                                        lse, loss_rows, loss_sum, M, V);
+                                                        lse, loss_rows, loss_sum, M, V, sum_scale);
     B200_RETURN_LAUNCH_STATUS("ce_finalize");
 }
 

@@ -232,3 +232,31 @@ extern "C" int b200_incr_int(int* p, int delta, cudaStream_t st) {
     incr_kernel<<<1, 1, 0, st>>>(p, delta);
     B200_RETURN_LAUNCH_STATUS("incr_int");
 }
+
+// seq[b, col] = next[b]   (col = *pos_dev + 1 when pos_dev is given)
+__global__ void scatter_tokens_kernel(const long long* next, long long* seq, int B, long long ld, int col,
+                                      const int* pos_dev) {
+    if (pos_dev != nullptr) col = *pos_dev + 1;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) seq[(size_t)b * ld + col] = next[b];
+}
+extern "C" int b200_scatter_tokens(const long long* next, long long* seq, int B, long long ld, int col,
+                                   const int* pos_dev, cudaStream_t st) {
+    scatter_tokens_kernel<<<(B + 127) / 128, 128, 0, st>>>(next, seq, B, ld, col, pos_dev);
+    B200_RETURN_LAUNCH_STATUS("scatter_tokens");
+}
+
+// out[b, :] = in[(b * T + T - 1), :]  - last-position rows for the last-token-only LM head
+__global__ void gather_last_rows_kernel(const uint4* in, uint4* out, int B, int T, int row_chunks) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < B * row_chunks) {
+        const int b = i / row_chunks, c = i % row_chunks;
+        out[(size_t)b * row_chunks + c] = in[((size_t)b * T + T - 1) * row_chunks + c];
+    }
+}
+extern "C" int b200_gather_last_rows(const void* in, void* out, int B, int T, int row_bytes, cudaStream_t st) {
+    B200_REQUIRE(row_bytes % 16 == 0, "gather_last_rows: row_bytes must be a multiple of 16");
+    const int rc = row_bytes / 16;
+    gather_last_rows_kernel<<<(B * rc + 255) / 256, 256, 0, st>>>((const uint4*)in, (uint4*)out, B, T, rc);
+    B200_RETURN_LAUNCH_STATUS("gather_last_rows");
+}

@@ -36,7 +36,7 @@ __device__ __forceinline__ float group_sum(float v, float* sred, int wir, int gr
 }
 
 template <int VPL, int WPR>
-__global__ void __launch_bounds__(256) ln_fwd_kernel(float* __restrict__ x, const bf16* __restrict__ branch,
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const float* x, float* x_out, const bf16* __restrict__ branch,
                                                      const float* __restrict__ gamma,
                                                      const float* __restrict__ beta, bf16* __restrict__ out,
                                                      float* __restrict__ out_f32, float* __restrict__ mean_out,
@@ -51,7 +51,8 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(float* __restrict__ x, cons
     if (row >= M) return;  // whole group exits together
 
     float4 v[VPL];
-    float4* xr = reinterpret_cast<float4*>(x + (size_t)row * D4 * 4);
+    const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * D4 * 4);
+    float4* xo = reinterpret_cast<float4*>(x_out + (size_t)row * D4 * 4);  // may alias x
 #pragma unroll
     for (int i = 0; i < VPL; ++i) v[i] = xr[wir * 32 + lane + i * 32 * WPR];
     if (branch != nullptr) {
@@ -61,7 +62,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(float* __restrict__ x, cons
             uint2 u = ldg_stream_u2(br + wir * 32 + lane + i * 32 * WPR);
             float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y);
             v[i].x += a.x; v[i].y += a.y; v[i].z += b.x; v[i].w += b.y;
-            xr[wir * 32 + lane + i * 32 * WPR] = v[i];
+            xo[wir * 32 + lane + i * 32 * WPR] = v[i];
         }
     }
     float s = 0.f;
@@ -240,14 +241,16 @@ extern "C" int b200_ln_supported(int d) {
     return ln_cfg(d, &c) ? 1 : 0;
 }
 
-extern "C" int b200_ln_fwd(float* x, const void* branch, const float* gamma, const float* beta, void* out_bf16,
-                           float* out_f32, float* mean, float* rstd, int M, int d, float eps, cudaStream_t st) {
+extern "C" int b200_ln_fwd(const float* x, const void* branch, float* x_out, const float* gamma, const float* beta,
+                           void* out_bf16, float* out_f32, float* mean, float* rstd, int M, int d, float eps,
+                           cudaStream_t st) {
+    B200_REQUIRE(branch == nullptr || x_out != nullptr, "ln_fwd: x_out is required when a branch is added");
     LnCfg cfg;
     B200_REQUIRE(ln_cfg(d, &cfg), "ln_fwd: unsupported width d=%d", d);
     if (M <= 0) return 0;
     const int G = 8 / cfg.wpr;
     const int grid = (M + G - 1) / G;
-    LN_DISPATCH_ALL((ln_fwd_kernel<VPL, WPR><<<grid, 256, 0, st>>>(x, (const bf16*)branch, gamma, beta,
+    LN_DISPATCH_ALL((ln_fwd_kernel<VPL, WPR><<<grid, 256, 0, st>>>(x, x_out, (const bf16*)branch, gamma, beta,
                                                                    (bf16*)out_bf16, out_f32, mean, rstd, M, eps)))
     B200_RETURN_LAUNCH_STATUS("ln_fwd");
 }

@@ -40,9 +40,9 @@ int b200_embed_bwd(const long long* idx, const float* dx, float* dwte, float* dw
 
 /* ---- fused residual-add + LayerNorm (ref: src/models/transformer_block.py:44,46; transformer.py:70) */
 int b200_ln_supported(int d);
-/* if branch: x += branch (fp32 residual updated in place); out = LN(x) * gamma + beta.
+/* r = x (+ branch, then stored to x_out, which may alias x); out = LN(r) * gamma + beta.
  * out_bf16 / out_f32 / mean / rstd may each be null. */
-int b200_ln_fwd(float* x, const void* branch, const float* gamma, const float* beta, void* out_bf16, float* out_f32, float* mean, float* rstd, int M, int d, float eps, cudaStream_t st);
+int b200_ln_fwd(const float* x, const void* branch, float* x_out, const float* gamma, const float* beta, void* out_bf16, float* out_f32, float* mean, float* rstd, int M, int d, float eps, cudaStream_t st);
 int b200_ln_bwd_nparts(int M, int d);
 /* dx_out = (dx_in or 0) + LN-backward(dy); dx_bf16 = bf16(dx_out) (nullable); dgamma/dbeta (+)=;
  * colsum (nullable) (+)= column sums of dx_in.  `partial` is scratch of
@@ -61,14 +61,15 @@ int b200_gemm_pick_bn(int M, int N, int K, int out_f32);
 int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn_override, int split_k, cudaStream_t st);
 
 /* ---- fused AdamW (ref: scripts/train_transformer.py:92,126 torch.optim.AdamW defaults) -------
- * hyper (device, 8 floats) = lr, beta1, beta2, eps, weight_decay, bias_correction1,
- * sqrt(bias_correction2), grad_scale.  p_bf16 (nullable) receives the bf16 shadow weights. */
+ * hyper (device, 8 floats) = 1 - lr*weight_decay, beta2, 1 - beta1, 1 - beta2, lr / bias_correction1,
+ * sqrt(bias_correction2), eps, grad_scale (derive them in double on the host: ops.adamw_hyper).
+ * p_bf16 (nullable) receives the bf16 shadow weights. */
 int b200_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, const float* hyper, long long n, cudaStream_t st);
 
 /* ---- softmax cross-entropy on bf16 logits (ref: src/models/transformer.py:74-77) ------------
  * finalize: combines the GEMM-epilogue statistics stats[n_tiles][M] into lse[M], reads the
- * target logit, writes loss_rows[M] = lse - logit[target] and loss_sum[0] (+)= sum of rows. */
-int b200_ce_finalize(const void* stats, int n_tiles, const void* logits, long long ld, const long long* targets, float* lse, float* loss_rows, float* loss_sum, int M, int V, cudaStream_t st);
+ * target logit, writes loss_rows[M] = lse - logit[target] and loss_sum[0] += sum_scale * sum of rows. */
+int b200_ce_finalize(const void* stats, int n_tiles, const void* logits, long long ld, const long long* targets, float* lse, float* loss_rows, float* loss_sum, int M, int V, float sum_scale, cudaStream_t st);
 /* in place: logits[m, v] = (exp(logits - lse[m]) - [v == target[m]]) * scale  (bf16), and
  * dbias[V] (+)= column sums of the result (ref: lm_head bias gradient) */
 int b200_ce_grad(void* logits, long long ld, const float* lse, const long long* targets, float* dbias, int M, int V, float scale, int accumulate, cudaStream_t st);
@@ -93,6 +94,10 @@ int b200_attn_decode(const void* qkv, const void* kcache, const void* vcache, vo
 int b200_sample(const void* logits, long long ld, long long* next, int B, int V, float temperature, int top_k, unsigned long long seed, unsigned long long step, const int* pos_dev, cudaStream_t st);
 
 int b200_incr_int(int* p, int delta, cudaStream_t st);
+/* seq[b, col] = next[b]  (col = *pos_dev + 1 when pos_dev is given) */
+int b200_scatter_tokens(const long long* next, long long* seq, int B, long long ld, int col, const int* pos_dev, cudaStream_t st);
+/* out[b, :] = in[b*T + T-1, :] : the last-position rows, for the last-token-only LM head */
+int b200_gather_last_rows(const void* in, void* out, int B, int T, int row_bytes, cudaStream_t st);
 
 #ifdef __cplusplus
 }

@@ -129,7 +129,7 @@ class ParamLayout:
             keys += [p + "ln1.weight", p + "ln1.bias"]
             for h in range(self.H):
                 q = p + f"attn.heads.{h}."
-                keys += [q + "key.weight", q + "query.weight", q + "value.weight", q + "tril"]
+                keys += [q + "tril", q + "key.weight", q + "query.weight", q + "value.weight"]  # buffers first
             keys += [p + "ln2.weight", p + "ln2.bias", p + "mlp.hidden.weight",
                      p + "mlp.hidden.bias", p + "mlp.proj.weight", p + "mlp.proj.bias"]
         keys += ["layer_norm.weight", "layer_norm.bias", "lm_head.weight", "lm_head.bias"]

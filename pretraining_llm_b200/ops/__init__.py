@@ -26,9 +26,16 @@ def _p(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
+LAUNCHES = 0   # kernels of this library enqueued so far (bench.py reports the count per timed region)
+
+_KERNELS_PER_CALL = {"embed_bwd": 2, "ln_bwd": 2, "attn_bwd": 3}
+
+
 def _chk(rc: int, what: str) -> None:
+    global LAUNCHES
     if rc != 0:
         lib.check(rc, what)
+    LAUNCHES += _KERNELS_PER_CALL.get(what, 1)
 
 
 # ------------------------------------------------------------------------------------------ GEMM
@@ -105,16 +112,18 @@ def embed_bwd(idx, dx, dwte, dwpe, accumulate: bool = False):
          "embed_bwd")
 
 
-def ln_fwd(x, gamma, beta, *, branch=None, out=None, out_f32=None, mean=None, rstd=None, eps: float = 1e-5,
-           want_stats: bool = True):
-    """x (fp32 [M,d], updated in place when branch is given) -> bf16 LN output (+ mean, rstd)."""
+def ln_fwd(x, gamma, beta, *, branch=None, x_out=None, out=None, out_f32=None, mean=None, rstd=None,
+           eps: float = 1e-5, want_stats: bool = True):
+    """r = x (+ branch -> stored to x_out, default in place) -> bf16 LN(r) (+ mean, rstd)."""
+    if branch is not None and x_out is None:
+        x_out = x
     M, d = x.shape
     if out is None and out_f32 is None:
         out = torch.empty(M, d, device=x.device, dtype=BF16)
     if want_stats and mean is None:
         mean = torch.empty(M, device=x.device, dtype=F32)
         rstd = torch.empty(M, device=x.device, dtype=F32)
-    _chk(lib.load().b200_ln_fwd(_p(x), _p(branch), _p(gamma), _p(beta), _p(out), _p(out_f32), _p(mean), _p(rstd),
+    _chk(lib.load().b200_ln_fwd(_p(x), _p(branch), _p(x_out), _p(gamma), _p(beta), _p(out), _p(out_f32), _p(mean), _p(rstd),
                                 M, d, eps, _st()), "ln_fwd")
     return out if out is not None else out_f32, mean, rstd
 
@@ -144,14 +153,14 @@ def adamw_hyper(lr: float, step: int, beta1=0.9, beta2=0.999, eps=1e-8, weight_d
     """The 8 floats b200_adamw reads (same derivations as torch.optim.AdamW's single step)."""
     bc1 = 1.0 - beta1 ** step
     bc2 = 1.0 - beta2 ** step
-    return [lr, beta1, beta2, eps, weight_decay, bc1, math.sqrt(bc2), grad_scale]
+    return [1.0 - lr * weight_decay, beta2, 1.0 - beta1, 1.0 - beta2, lr / bc1, math.sqrt(bc2), eps, grad_scale]
 
 
 # ------------------------------------------------------------------------------------------ CE
-def ce_finalize(stats, n_tiles, logits, targets, lse, loss_rows, loss_sum, V):
+def ce_finalize(stats, n_tiles, logits, targets, lse, loss_rows, loss_sum, V, sum_scale: float = 1.0):
     M = logits.shape[0]
     _chk(lib.load().b200_ce_finalize(_p(stats), n_tiles, _p(logits), logits.stride(0), _p(targets), _p(lse),
-                                     _p(loss_rows), _p(loss_sum), M, V, _st()), "ce_finalize")
+                                     _p(loss_rows), _p(loss_sum), M, V, float(sum_scale), _st()), "ce_finalize")
 
 
 def ce_grad(logits, lse, targets, dbias, V, scale: float, accumulate: bool = False):
@@ -204,3 +213,14 @@ def incr_int(t: torch.Tensor, delta: int = 1):
 
 def l2_flush(buf: torch.Tensor):
     _chk(lib.load().b200_l2_flush(_p(buf), buf.numel() * buf.element_size(), _st()), "l2_flush")
+
+
+def scatter_tokens(next_tok, seq, col=0, pos_dev=None):
+    B = next_tok.shape[0]
+    _chk(lib.load().b200_scatter_tokens(_p(next_tok), _p(seq), B, seq.stride(0), col, _p(pos_dev), _st()),
+         "scatter_tokens")
+
+
+def gather_last_rows(x, out, B, T):
+    _chk(lib.load().b200_gather_last_rows(_p(x), _p(out), B, T, x.shape[-1] * x.element_size(), _st()),
+         "gather_last_rows")

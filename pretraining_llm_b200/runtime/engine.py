@@ -1,0 +1,346 @@
+"""Engine: the static kernel schedule that runs a ``Transformer`` on a B200.
+
+One ``Engine`` owns, for one model:
+  * the flat fp32 master parameters (shared with the nn.Module's Parameters), a flat bf16 shadow
+    copy the GEMMs read, a flat fp32 gradient buffer and the flat AdamW moments;
+  * per-(B, T) workspaces with every activation the backward pass needs, allocated once;
+  * the forward / backward / optimizer launch sequences (hand-written sm_100a kernels only - no
+    autograd, no cuBLAS, no Triton on this path) and CUDA graphs of whole training steps.
+
+Forward per block (reference src/models/transformer_block.py:44-46 + attention.py + mlp.py):
+    h1 = LN1(r_a)                       ln_fwd            (r_a = residual stream, fp32)
+    qkv = h1 @ Wqkv^T                   gemm              (packed [Wq; Wk; Wv])
+    att = causal_attention(qkv)         attn_fwd          (flash, no T x T tensor)
+    r_b = r_a + att ; h2 = LN2(r_b)     ln_fwd (fused residual add)
+    act = relu(h2 @ W1^T + b1)          gemm (+bias +ReLU epilogue)
+    mo  = act @ W2^T + b2               gemm (+bias epilogue)
+    r_a' = r_b + mo ; h1' = LN1'(r_a')  ln_fwd of the NEXT block (or the final LayerNorm)
+LM head (reference transformer.py:70-77): logits = hf @ Wlm^T + b with softmax statistics in the
+GEMM epilogue, ce_finalize -> loss; backward turns the bf16 logits into dlogits in place.
+
+Backward mirrors it with dgrad GEMMs (B operand MN-major, ReLU mask fused in the epilogue),
+wgrad GEMMs (both operands MN-major, fp32 straight into the flat gradient buffer), flash
+attention backward and the fused LN-backward (+ residual-gradient add + bias-gradient column
+sums).  See DESIGN.md for the buffer plan.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from .. import ops
+
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+class Workspace:
+    """All activations and scratch for one (B, T) shape."""
+
+    def __init__(self, eng: "Engine", B: int, T: int, train: bool):
+        lay = eng.layout
+        d, H, hs, L, V = lay.d, lay.H, lay.hs, lay.L, lay.V
+        M = B * T
+        dev = eng.device
+        self.B, self.T, self.M, self.train = B, T, M, train
+        Ls = L if train else 1                      # inference reuses slot 0 for every layer
+        e = lambda *s, dt=BF16: torch.empty(*s, device=dev, dtype=dt)
+        self.resid_a = e(Ls + 1, M, d, dt=F32)      # [l] = input of block l; [Ls] = input of final LN
+        self.resid_b = e(Ls, M, d, dt=F32)
+        self.h1, self.h2 = e(Ls, M, d), e(Ls, M, d)
+        self.qkv = e(Ls, M, 3 * d)
+        self.att = e(Ls, M, d)
+        self.act = e(Ls, M, 4 * d)
+        self.mlp_out = e(M, d)
+        self.lse = e(Ls, B, H, T, dt=F32)
+        self.ln_stats = e(2 * Ls + 1, 2, M, dt=F32)  # (mean, rstd) for ln1/ln2 of each layer + final
+        self.hf = e(M, d)
+        self.Vp = (V + 7) // 8 * 8
+        self.logits = e(M, self.Vp)
+        self.nt = (V + 255) // 256
+        self.ce_stats = e(self.nt, M, 2, dt=F32)
+        self.ce_lse = e(M, dt=F32)
+        self.loss_rows = e(M, dt=F32)
+        self.loss = torch.zeros(1, device=dev, dtype=F32)
+        self.idx = torch.zeros(B, T, device=dev, dtype=torch.int64)
+        self.tgt = torch.zeros(B, T, device=dev, dtype=torch.int64)
+        if train:
+            self.dx = e(M, d, dt=F32)
+            self.dx_bf16 = e(M, d)
+            self.dh = e(M, 4 * d)
+            self.dqkv = e(M, 3 * d)
+            self.dtmp = e(M, d)
+            self.delta = e(B, H, T, dt=F32)
+            self.dq_acc = torch.zeros(M, d, device=dev, dtype=F32)
+            self.ln_partial = e(max(ops.ln_bwd_nparts(M, d), 1) * 3 * d, dt=F32)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+
+
+class Engine:
+    def __init__(self, model):
+        self.model = model
+        self.layout = model.layout
+        self.flat: torch.Tensor = model._flat
+        assert self.flat.is_cuda and self.flat.dtype == F32
+        self.device = self.flat.device
+        if not ops.lib.load().b200_ln_supported(self.layout.d):
+            raise ValueError(f"n_embed={self.layout.d} is not supported by the LayerNorm kernels")
+        if self.layout.hs not in (64, 128):
+            raise ValueError(f"head size {self.layout.hs} is not supported by the attention kernels (64 or 128)")
+        n = self.layout.total
+        self.wb = torch.empty(n, device=self.device, dtype=BF16)     # bf16 shadow weights
+        self._wb_version = -1
+        self.grad: Optional[torch.Tensor] = None
+        self.exp_avg: Optional[torch.Tensor] = None
+        self.exp_avg_sq: Optional[torch.Tensor] = None
+        self.step_count = 0
+        self.hyper = torch.zeros(8, device=self.device, dtype=F32)
+        self.hyper_host = torch.zeros(8, dtype=F32).pin_memory()
+        self.betas, self.eps, self.weight_decay = (0.9, 0.999), 1e-8, 0.01   # torch.optim.AdamW defaults
+        self.ws: Dict[Tuple[int, int, bool], Workspace] = {}
+        self.dp = None                     # parallel.dp.DataParallel, set by attach_dp()
+        self.launches_per_step = 0
+        self._gen = None
+
+    # ------------------------------------------------------------------ parameters
+    def W(self, name: str) -> torch.Tensor:       # bf16 shadow view
+        return self.layout.view(self.wb, name)
+
+    def P(self, name: str) -> torch.Tensor:       # fp32 master view
+        return self.layout.view(self.flat, name)
+
+    def G(self, name: str) -> torch.Tensor:       # fp32 gradient view
+        return self.layout.view(self.grad, name)
+
+    def params_changed(self) -> None:
+        self._wb_version = -1
+
+    def sync_weights(self) -> None:
+        """Refresh the bf16 shadow if the fp32 masters were modified by anyone but our AdamW."""
+        v = self.flat._version
+        if v != self._wb_version:
+            ops.cast_bf16(self.flat, self.wb)
+            self._wb_version = v
+
+    def ensure_grad(self) -> None:
+        if self.grad is None:
+            self.grad = torch.zeros_like(self.flat)
+
+    def ensure_opt_state(self) -> None:
+        if self.exp_avg is None:
+            self.exp_avg = torch.zeros_like(self.flat)
+            self.exp_avg_sq = torch.zeros_like(self.flat)
+
+    def workspace(self, B: int, T: int, train: bool) -> Workspace:
+        key = (B, T, train)
+        w = self.ws.get(key)
+        if w is None:
+            if len(self.ws) >= 4:          # keep memory bounded when shapes vary (generation prefill)
+                for k in [k for k in self.ws if not k[2]][:2]:
+                    del self.ws[k]
+            w = self.ws[key] = Workspace(self, B, T, train)
+        return w
+
+    # ------------------------------------------------------------------ forward
+    def _blocks_forward(self, w: Workspace, kv=None, pos0: int = 0) -> None:
+        lay = self.layout
+        B, T, L, H, hs = w.B, w.T, lay.L, lay.H, lay.hs
+        for l in range(L):
+            s = l if w.train else 0
+            pre = f"attn_blocks.{l}."
+            ra_in = w.resid_a[s]
+            st1, st2 = w.ln_stats[2 * s], w.ln_stats[2 * s + 1]
+            if l == 0:
+                ops.ln_fwd(ra_in, self.P(pre + "ln1.weight"), self.P(pre + "ln1.bias"), out=w.h1[s],
+                           mean=st1[0], rstd=st1[1])
+            else:
+                sp = (l - 1) if w.train else 0
+                ops.ln_fwd(w.resid_b[sp], self.P(pre + "ln1.weight"), self.P(pre + "ln1.bias"), branch=w.mlp_out,
+                           x_out=ra_in, out=w.h1[s], mean=st1[0], rstd=st1[1])
+            ops.gemm(w.h1[s], self.W(pre + "attn.wqkv"), out=w.qkv[s])
+            if kv is not None:
+                ops.kv_append(w.qkv[s], kv[0][l], kv[1][l], B, T, H, hs, kv[0].shape[3], pos0=pos0)
+            ops.attn_fwd(w.qkv[s], B, T, H, hs, out=w.att[s], lse=w.lse[s])
+            ops.ln_fwd(ra_in, self.P(pre + "ln2.weight"), self.P(pre + "ln2.bias"), branch=w.att[s],
+                       x_out=w.resid_b[s], out=w.h2[s], mean=st2[0], rstd=st2[1])
+            ops.gemm(w.h2[s], self.W(pre + "mlp.hidden.weight"), out=w.act[s], bias=self.P(pre + "mlp.hidden.bias"),
+                     relu=True)
+            ops.gemm(w.act[s], self.W(pre + "mlp.proj.weight"), out=w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
+        sl = (L - 1) if w.train else 0
+        sf = L if w.train else 1
+        stf = w.ln_stats[2 * (L if w.train else 1)]
+        ops.ln_fwd(w.resid_b[sl], self.P("layer_norm.weight"), self.P("layer_norm.bias"), branch=w.mlp_out,
+                   x_out=w.resid_a[sf], out=w.hf, mean=stf[0], rstd=stf[1])
+
+    def forward(self, idx: torch.Tensor, targets: Optional[torch.Tensor] = None, *, train: bool = False,
+                loss_scale: float = 1.0):
+        """Run the model.  Returns (workspace, logits view (B,T,V) bf16, loss 0-dim fp32 or None).
+        ``train=True`` keeps every activation for ``backward``."""
+        B, T = idx.shape
+        if T > self.layout.ctx:
+            raise IndexError(f"sequence length {T} exceeds context_length {self.layout.ctx}")
+        w = self.workspace(B, T, train)
+        self.sync_weights()
+        if idx.data_ptr() != w.idx.data_ptr():
+            w.idx.copy_(idx)
+        if targets is not None and targets.data_ptr() != w.tgt.data_ptr():
+            w.tgt.copy_(targets.reshape(B, T))
+        self._forward_ws(w, targets is not None, loss_scale)
+        V = self.layout.V
+        logits = w.logits[:, :V].view(B, T, V)
+        return w, logits, (w.loss[0] if targets is not None else None)
+
+    def _forward_ws(self, w: Workspace, with_loss: bool, loss_scale: float = 1.0) -> None:
+        lay = self.layout
+        ops.embed_fwd(w.idx, self.P("token_embed.weight"), self.P("position_embed.weight"), out=w.resid_a[0])
+        self._blocks_forward(w)
+        V = lay.V
+        ops.gemm(w.hf, self.W("lm_head.weight"), out=w.logits[:, :V], bias=self.P("lm_head.bias"),
+                 stats=w.ce_stats if with_loss else None, bn=256)
+        if with_loss:
+            w.loss.zero_()
+            ops.ce_finalize(w.ce_stats, w.nt, w.logits, w.tgt.view(-1), w.ce_lse, w.loss_rows, w.loss, V,
+                            sum_scale=loss_scale / w.M)
+
+    # ------------------------------------------------------------------ backward
+    def backward(self, w: Workspace, *, grad_scale: float = 1.0, accumulate: bool = False) -> None:
+        """Gradients of (grad_scale * mean CE) w.r.t. every parameter -> the flat fp32 grad buffer."""
+        assert w.train, "backward needs a training workspace"
+        self.ensure_grad()
+        lay = self.layout
+        B, T, M, L, H, hs, V = w.B, w.T, w.M, lay.L, lay.H, lay.hs, lay.V
+        fm = 1 if accumulate else 0
+        if not accumulate:
+            self.G("token_embed.weight").zero_()     # scatter-add target
+        # LM head + CE
+        dlog = w.logits[:, :V]
+        ops.ce_grad(dlog, w.ce_lse, w.tgt.view(-1), self.G("lm_head.bias"), V, grad_scale / M, accumulate=accumulate)
+        ops.gemm(dlog, w.hf, out=self.G("lm_head.weight"), a_mn=True, b_mn=True, f32_mode=fm)
+        ops.gemm(dlog, self.W("lm_head.weight"), out=w.dtmp, b_mn=True)
+        stf = w.ln_stats[2 * L]
+        ops.ln_bwd(w.dtmp, w.resid_a[L], stf[0], stf[1], self.P("layer_norm.weight"), self.G("layer_norm.weight"),
+                   self.G("layer_norm.bias"), dx_out=w.dx, dx_bf16=w.dx_bf16, partial=w.ln_partial, accumulate=accumulate)
+        for l in reversed(range(L)):
+            pre = f"attn_blocks.{l}."
+            st1, st2 = w.ln_stats[2 * l], w.ln_stats[2 * l + 1]
+            # ---- MLP
+            ops.gemm(w.dx_bf16, w.act[l], out=self.G(pre + "mlp.proj.weight"), a_mn=True, b_mn=True, f32_mode=fm)
+            ops.gemm(w.dx_bf16, self.W(pre + "mlp.proj.weight"), out=w.dh, b_mn=True, mask=w.act[l])
+            ops.colsum(w.dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
+            ops.gemm(w.dh, w.h2[l], out=self.G(pre + "mlp.hidden.weight"), a_mn=True, b_mn=True, f32_mode=fm)
+            ops.gemm(w.dh, self.W(pre + "mlp.hidden.weight"), out=w.dtmp, b_mn=True)
+            ops.ln_bwd(w.dtmp, w.resid_b[l], st2[0], st2[1], self.P(pre + "ln2.weight"), self.G(pre + "ln2.weight"),
+                       self.G(pre + "ln2.bias"), dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16,
+                       colsum_out=self.G(pre + "mlp.proj.bias"), partial=w.ln_partial, accumulate=accumulate)
+            # ---- attention
+            ops.attn_bwd(w.qkv[l], w.att[l], w.dx_bf16, w.lse[l], B, T, H, hs, dqkv=w.dqkv, delta=w.delta,
+                         dq_acc=w.dq_acc)
+            ops.gemm(w.dqkv, w.h1[l], out=self.G(pre + "attn.wqkv"), a_mn=True, b_mn=True, f32_mode=fm)
+            ops.gemm(w.dqkv, self.W(pre + "attn.wqkv"), out=w.dtmp, b_mn=True)
+            ops.ln_bwd(w.dtmp, w.resid_a[l], st1[0], st1[1], self.P(pre + "ln1.weight"), self.G(pre + "ln1.weight"),
+                       self.G(pre + "ln1.bias"), dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16, partial=w.ln_partial,
+                       accumulate=accumulate)
+            if self.dp is not None:
+                self.dp.bucket_ready(l)
+        ops.embed_bwd(w.idx, w.dx, self.G("token_embed.weight"), self.G("position_embed.weight")[:T],
+                      accumulate=accumulate)
+        if not accumulate and T < lay.ctx:
+            self.G("position_embed.weight")[T:].zero_()
+
+    # ------------------------------------------------------------------ optimizer
+    def set_hyper(self, lr: float, grad_scale: float = 1.0) -> None:
+        """Stage AdamW scalars for the NEXT optimizer launch (also read by graph replays)."""
+        self.step_count += 1
+        vals = ops.adamw_hyper(lr, self.step_count, self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                               grad_scale)
+        self.hyper_host.copy_(torch.tensor(vals, dtype=F32))
+        self.hyper.copy_(self.hyper_host, non_blocking=True)
+        self.lr = lr
+
+    def optimizer_step(self) -> None:
+        """Fused AdamW over the whole flat buffer (fp32 masters + bf16 shadow) using staged scalars."""
+        self.ensure_opt_state()
+        if self.dp is not None:
+            self.dp.reduce_and_step()
+        else:
+            ops.adamw(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.wb, self.hyper)
+        # our kernel wrote the masters and the shadow together: keep them marked in sync
+        self._wb_version = self.flat._version
+
+    def zero_grad(self) -> None:
+        if self.grad is not None:
+            self.grad.zero_()
+
+    # ------------------------------------------------------------------ whole training step
+    def train_step(self, idx: torch.Tensor, targets: torch.Tensor, lr: float, *, use_graph: bool = True
+                   ) -> torch.Tensor:
+        """forward + backward + (gradient reduction) + AdamW.  Returns the loss as a 0-dim device
+        tensor (no host sync).  From the second call with the same shape the step is one CUDA
+        graph replay."""
+        B, T = idx.shape
+        w = self.workspace(B, T, True)
+        self.ensure_grad()
+        self.ensure_opt_state()
+        self.sync_weights()
+        w.idx.copy_(idx, non_blocking=True)
+        w.tgt.copy_(targets.reshape(B, T), non_blocking=True)
+        self.set_hyper(lr)
+        if use_graph and w.graph is not None:
+            w.graph.replay()
+        elif use_graph and getattr(w, "warm", False) and self.dp is None:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._step_body(w)
+            w.graph = g
+            g.replay()
+        else:
+            self._step_body(w)
+            w.warm = True
+        return w.loss[0]
+
+    def _step_body(self, w: Workspace) -> None:
+        self._forward_ws(w, True)
+        self.backward(w)
+        self.optimizer_step()
+
+    # ------------------------------------------------------------------ nn.Module facade path
+    def module_forward(self, idx: torch.Tensor, targets: Optional[torch.Tensor]):
+        grad_mode = torch.is_grad_enabled() and targets is not None and self.model.training
+        idx = idx.contiguous()
+        if idx.dtype != torch.int64:
+            idx = idx.long()
+        if targets is not None:
+            targets = targets.contiguous().long()
+        if not grad_mode:
+            _, logits, loss = self.forward(idx, targets, train=False)
+            return logits, (loss.clone() if loss is not None else None)
+        params = [p for _, p in self.model.named_parameters()]
+        loss, logits = _EngineLoss.apply(self, idx, targets, *params)
+        return logits, loss
+
+    # ------------------------------------------------------------------ generation
+    def generate(self, idx, max_new_tokens, **kw):
+        from .generation import Generator
+        if self._gen is None:
+            self._gen = Generator(self)
+        return self._gen.generate(idx, max_new_tokens, **kw)
+
+
+class _EngineLoss(torch.autograd.Function):
+    """One autograd node for the whole model: forward runs the engine's forward schedule, backward
+    runs its backward schedule and hands each Parameter a view of the flat gradient buffer."""
+
+    @staticmethod
+    def forward(ctx, eng: Engine, idx, targets, *params):
+        w, logits, loss = eng.forward(idx, targets, train=True)
+        ctx.eng, ctx.w = eng, w
+        ctx.mark_non_differentiable(logits)
+        return loss.clone(), logits
+
+    @staticmethod
+    def backward(ctx, gloss, _glogits):
+        eng: Engine = ctx.eng
+        eng.backward(ctx.w, grad_scale=float(gloss))
+        names = [n for n, _ in eng.model.named_parameters()]
+        return (None, None, None) + tuple(eng.layout.view(eng.grad, n) for n in names)

@@ -1,0 +1,327 @@
+"""CPU tier: the reference's public surface, checked against the reference's own modules."""
+import math
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from pretraining_llm_b200.config import PRESETS, apply_overrides, default_config, model_args, validate
+from pretraining_llm_b200.data.loader import get_batch_iterator
+from pretraining_llm_b200.models import Block, Head, MLP, MultiHeadAttention, Transformer
+from pretraining_llm_b200.models.layout import ParamLayout
+from pretraining_llm_b200.runtime.trainer import Trainer, get_lr
+
+REF_KEYS = ["vocab_size", "context_length", "n_embed", "n_head", "n_blocks", "train_path", "dev_path",
+            "t_batch_size", "t_context_length", "t_train_steps", "t_eval_steps", "t_eval_iters",
+            "t_lr_decay_step", "t_lr", "t_lr_decayed", "t_out_path", "device"]
+
+TINY = dict(n_head=4, n_embed=64, context_length=32, vocab_size=101)
+
+
+# ------------------------------------------------------------------------------------------ config
+def test_config_superset_of_reference():
+    from baseline.ref_import import import_reference_config
+    ref = import_reference_config()
+    keys = list(ref.default_config) if ref is not None else REF_KEYS
+    assert keys == REF_KEYS
+    assert list(default_config)[:17] == REF_KEYS            # same keys, same order
+    for k in ("val_path", "dtype", "ddp_backend", "dataset_name", "tokenizer_name", "seed", "grad_accum_steps",
+              "dp_mode"):
+        assert k in default_config
+    if ref is not None:
+        for k in REF_KEYS:
+            if k not in ("train_path", "dev_path"):          # .h5 -> .bin on purpose (defect D6)
+                assert default_config[k] == ref.default_config[k], k
+
+
+def test_config_overrides_and_validation():
+    cfg = dict(default_config)
+    apply_overrides(cfg, ["preset=gpt2-small", "t_lr=1e-3", "synthetic_data=true", "t_train_steps=7"])
+    assert cfg["n_embed"] == 768 and cfg["t_lr"] == 1e-3 and cfg["synthetic_data"] is True and cfg["t_train_steps"] == 7
+    assert set(model_args(cfg)) == {"vocab_size", "n_embed", "n_head", "n_blocks", "context_length"}
+    with pytest.raises(KeyError):
+        apply_overrides(cfg, ["nope=1"])
+    bad = dict(cfg, n_head=7)
+    with pytest.raises(ValueError):
+        validate(bad)
+    assert set(PRESETS) >= {"tiny", "gpt2-small", "1.3b"}
+
+
+# ------------------------------------------------------------------------------------------ LR schedule
+def test_lr_schedule_matches_reference():
+    cfg = dict(default_config, t_train_steps=1000, t_lr=5e-4)
+
+    def ref_lr(it):   # reference scripts/train_transformer.py:43-49
+        if it < cfg["t_train_steps"] * 0.1:
+            return cfg["t_lr"] * it / (cfg["t_train_steps"] * 0.1)
+        return cfg["t_lr"]
+
+    for it in (0, 1, 50, 99, 100, 101, 999):
+        assert get_lr(it, cfg) == ref_lr(it)
+    assert get_lr(0, cfg) == 0.0
+    dec = dict(cfg, lr_schedule="decay", t_lr_decay_step=500, t_lr_decayed=5e-5)
+    assert get_lr(499, dec) == 5e-4 and get_lr(500, dec) == 5e-5
+
+
+# ------------------------------------------------------------------------------------------ data loader
+def test_batch_iterator_contract(tmp_path):
+    data = np.arange(5000, dtype=np.uint16)
+    p = tmp_path / "tok.bin"
+    data.tofile(p)
+    it = get_batch_iterator(str(p), 4, 16)
+    x, y = next(it)
+    assert x.shape == (4, 16) and y.shape == (4, 16) and x.dtype == torch.int64 and y.dtype == torch.int64
+    assert torch.equal(x[:, 1:], y[:, :-1])                  # y is x shifted by one token
+    assert torch.equal(y - x, torch.ones_like(x))            # contiguous windows of the stream
+    # rank sharding: contiguous slabs, disjoint between ranks (the reference strides, defect D9)
+    xs = [next(get_batch_iterator(str(p), 64, 16, "cpu", True, r, 4))[0] for r in range(4)]
+    for r in range(4):
+        assert xs[r].min() >= r * 1250 and xs[r].max() < (r + 1) * 1250
+    # different ranks draw different offsets; same (seed, rank) reproduces
+    a = next(get_batch_iterator(str(p), 8, 16, "cpu", True, 1, 4, seed=5))[0]
+    b = next(get_batch_iterator(str(p), 8, 16, "cpu", True, 1, 4, seed=5))[0]
+    assert torch.equal(a, b)
+
+
+def test_batch_iterator_synthetic_and_validation(tmp_path):
+    x, y = next(get_batch_iterator(None, 3, 9, vocab_size=50))
+    assert x.shape == (3, 9) and int(x.max()) < 50 and torch.equal(x[:, 1:], y[:, :-1])
+    with pytest.raises(FileNotFoundError):
+        next(get_batch_iterator(str(tmp_path / "missing.bin"), 2, 4))
+    h5 = tmp_path / "x.h5"
+    h5.write_bytes(b"\x89HDF\r\n\x1a\n" + b"\0" * 64)
+    with pytest.raises(ValueError):
+        next(get_batch_iterator(str(h5), 2, 4))
+
+
+def test_reference_loader_signature_compatible():
+    import inspect
+    from baseline.ref_import import import_reference_data_loader
+    ref = import_reference_data_loader()
+    if ref is None:
+        pytest.skip("reference not available")
+    ref_params = list(inspect.signature(ref.get_batch_iterator).parameters)
+    ours = list(inspect.signature(get_batch_iterator).parameters)
+    assert ours[:len(ref_params)] == ref_params
+
+
+# ------------------------------------------------------------------------------------------ model vs reference
+@pytest.mark.parametrize("L", [1, 3])
+def test_same_seed_same_weights_and_logits(ref_models, L):
+    torch.manual_seed(11)
+    ours = Transformer(**TINY, N_BLOCKS=L)
+    torch.manual_seed(11)
+    ref = ref_models.Transformer(TINY["n_head"], TINY["n_embed"], TINY["context_length"], TINY["vocab_size"], L)
+    sd, rsd = ours.state_dict(), ref.state_dict()
+    assert list(sd) == list(rsd)                              # same keys, same order (incl. buffers)
+    for k in rsd:
+        assert sd[k].shape == rsd[k].shape and sd[k].dtype == rsd[k].dtype, k
+        assert torch.equal(sd[k], rsd[k]), k                 # bit-identical init from the same seed
+    idx = torch.randint(0, TINY["vocab_size"], (2, 20))
+    lo, loss_o = ours(idx, idx)
+    lr_, loss_r = ref(idx, idx)
+    assert torch.allclose(lo, lr_, atol=2e-5) and abs(loss_o.item() - loss_r.item()) < 1e-5
+    loss_o.backward()
+    loss_r.backward()
+    g_ref = ref.attn_blocks[0].attn.heads[2].key.weight.grad
+    g_ours = ours.attn_blocks[0].attn.head_weights(2)[0]
+    g_ours = ours.attn_blocks[0].attn.wqkv.grad[TINY["n_embed"] + 2 * 16: TINY["n_embed"] + 3 * 16]
+    assert torch.allclose(g_ours, g_ref, atol=1e-5)
+    assert torch.allclose(ours.lm_head.weight.grad, ref.lm_head.weight.grad, atol=1e-5)
+
+
+def test_ctor_accepts_both_spellings():
+    a = Transformer(**TINY, N_BLOCKS=2)
+    b = Transformer(**TINY, n_blocks=2)                        # the spelling the reference's script uses (D1)
+    assert a.N_BLOCKS == b.N_BLOCKS == 2
+    with pytest.raises(TypeError):
+        Transformer(**TINY)
+    with pytest.raises(IndexError):
+        a(torch.zeros(1, TINY["context_length"] + 1, dtype=torch.long))
+
+
+def test_checkpoint_cross_load_both_ways(ref_models, tmp_path):
+    torch.manual_seed(3)
+    ours = Transformer(**TINY, N_BLOCKS=2)
+    ref = ref_models.Transformer(TINY["n_head"], TINY["n_embed"], TINY["context_length"], TINY["vocab_size"], 2)
+    # ours -> file -> reference (strict)
+    p = tmp_path / "ck.pt"
+    torch.save({"model_state_dict": ours.state_dict()}, p)
+    ref.load_state_dict(torch.load(p)["model_state_dict"], strict=True)
+    idx = torch.randint(0, TINY["vocab_size"], (2, 12))
+    assert torch.allclose(ours(idx)[0], ref(idx)[0], atol=2e-5)
+    # reference -> ours, including torch.compile / DDP key prefixes (defect D11)
+    torch.manual_seed(4)
+    ref2 = ref_models.Transformer(TINY["n_head"], TINY["n_embed"], TINY["context_length"], TINY["vocab_size"], 2)
+    for prefix in ("", "_orig_mod.", "module._orig_mod.", "module."):
+        sd = {prefix + k: v for k, v in ref2.state_dict().items()}
+        ours.load_state_dict(sd, strict=True)
+        assert torch.allclose(ours(idx)[0], ref2(idx)[0], atol=2e-5)
+    with pytest.raises(RuntimeError):
+        bad = dict(ref2.state_dict())
+        bad.pop("lm_head.bias")
+        ours.load_state_dict(bad, strict=True)
+    # the tril keys share one storage: the file does not hold H*L masks
+    sd = ours.state_dict()
+    trils = [v for k, v in sd.items() if k.endswith(".tril")]
+    assert len({t.data_ptr() for t in trils}) == 1 and len(trils) == 2 * TINY["n_head"]
+    assert torch.equal(trils[0], torch.tril(torch.ones(32, 32)))
+    assert torch.equal(sd["pos_idxs"], torch.arange(32))
+
+
+def test_packed_layout_roundtrip_and_counts():
+    lay = ParamLayout(4, 64, 32, 101, 2)
+    d, V, ctx, L, H = 64, 101, 32, 2, 4
+    assert lay.num_params() == L * (11 * d * d + 9 * d) + 2 * V * d + V + ctx * d + 2 * d
+    assert len(lay.reference_keys()) == 1 + 2 + L * (4 + 4 * H + 4) + 2 + 2
+    assert len(lay.reference_param_names()) == 2 + L * (3 * H + 8) + 4
+    flat = torch.randn(lay.total)
+    sd = lay.to_reference_state_dict(flat)
+    flat2 = torch.zeros(lay.total)
+    lay.from_reference_state_dict(flat2, sd)
+    for n in lay.slots:
+        assert torch.equal(lay.view(flat, n), lay.view(flat2, n)), n
+    for s in lay.slots.values():
+        assert s.offset % 128 == 0
+    names = [b[0] for b in lay.buckets()]
+    assert names[0] == "head" and names[-1] == "embed" and names[1] == "block1"
+
+
+def test_module_api_parity(ref_models):
+    torch.manual_seed(0)
+    blk = Block(4, 64, 32)
+    x = torch.randn(2, 10, 64)
+    hid, res = blk.forward_embedding(x)
+    assert hid.shape == (2, 10, 256) and res.shape == (2, 10, 64)
+    assert torch.allclose(blk.mlp.project_embedding(hid) + res, blk(x), atol=1e-5)
+    mlp = MLP(64)
+    assert torch.allclose(mlp(x), mlp.project_embedding(mlp.forward_embedding(x)))
+    head = Head(16, 64, 32)
+    rhead = ref_models.Head(16, 64, 32)
+    rhead.load_state_dict({**{k: v for k, v in head.state_dict().items()}, "tril": torch.tril(torch.ones(32, 32))})
+    assert torch.allclose(head(x), rhead(x), atol=1e-5)
+    mha = MultiHeadAttention(4, 64, 32)
+    assert mha(x).shape == (2, 10, 64)
+    # forward_embedding equals the reference's for one block (defined for deeper models too, D12)
+    torch.manual_seed(5)
+    ours = Transformer(**TINY, N_BLOCKS=1)
+    ref = ref_models.Transformer(4, 64, 32, 101, 1)
+    ref.load_state_dict(ours.state_dict())
+    idx = torch.randint(0, 101, (2, 9))
+    a, b = ours.forward_embedding(idx)
+    c, d = ref.forward_embedding(idx)
+    assert torch.allclose(a, c, atol=1e-5) and torch.allclose(b, d, atol=1e-5)
+    deep = Transformer(**TINY, N_BLOCKS=3)
+    h, r = deep.forward_embedding(idx)
+    assert h.shape == (2, 9, 256) and r.shape == (2, 9, 64)
+
+
+# ------------------------------------------------------------------------------------------ generation
+def test_generate_kv_cache_equals_full_recompute():
+    from pretraining_llm_b200.runtime.torch_generate import generate_torch
+    torch.manual_seed(1)
+    m = Transformer(**TINY, N_BLOCKS=2).eval()
+    idx = torch.randint(0, 101, (3, 5))
+    g1 = torch.Generator().manual_seed(9)
+    g2 = torch.Generator().manual_seed(9)
+    a, la = generate_torch(m, idx, 20, use_cache=True, generator=g1, return_logits=True)
+    b, lb = generate_torch(m, idx, 20, use_cache=False, generator=g2, return_logits=True)
+    assert torch.equal(a, b)
+    for x, y in zip(la, lb):
+        assert torch.allclose(x, y, atol=1e-4)
+    # window overflow: 5 + 40 > ctx 32 -> falls back to the reference's sliding window
+    out = m.generate(idx, 40)
+    assert out.shape == (3, 45) and torch.equal(out[:, :5], idx)
+
+
+def test_generate_matches_reference_sampler(ref_models):
+    torch.manual_seed(2)
+    ours = Transformer(**TINY, N_BLOCKS=2).eval()
+    ref = ref_models.Transformer(4, 64, 32, 101, 2).eval()
+    ref.load_state_dict(ours.state_dict())
+    idx = torch.randint(0, 101, (2, 4))
+    torch.manual_seed(77)
+    r = ref.generate(idx, 12)
+    torch.manual_seed(77)
+    o = ours.generate(idx, 12)                                # default generator, same draws
+    assert torch.equal(o, r)
+
+
+# ------------------------------------------------------------------------------------------ trainer
+def _cpu_cfg(tmp_path, **kw):
+    cfg = dict(default_config)
+    cfg.update(dict(vocab_size=101, context_length=32, n_embed=64, n_head=4, n_blocks=2, t_batch_size=4,
+                    t_train_steps=6, t_eval_steps=3, t_eval_iters=2, t_lr=1e-2, device="cpu", dtype="float32",
+                    t_out_path=str(tmp_path / "models" / "m.pt"), synthetic_data=True))
+    cfg.update(kw)
+    return cfg
+
+
+def test_trainer_cpu_end_to_end(ref_models, tmp_path, capsys):
+    cfg = _cpu_cfg(tmp_path)
+    torch.manual_seed(0)
+    model = Transformer(**model_args(cfg))
+    it = get_batch_iterator("synthetic:101", 4, 32, seed=1)
+    tr = Trainer(model, it, get_batch_iterator("synthetic:101", 4, 32, seed=2), None, config=cfg)
+    tr.train()
+    out = capsys.readouterr().out
+    assert "Step 0: Train Loss=" in out and "Val Loss=" in out and "LR=0.00e+00" in out     # reference's line
+    ck = torch.load(cfg["t_out_path"], weights_only=False)
+    assert set(ck) >= {"model_state_dict", "optimizer_state_dict"}
+    # the reference's model AND torch's AdamW accept the checkpoint as is
+    ref = ref_models.Transformer(4, 64, 32, 101, 2)
+    ref.load_state_dict(ck["model_state_dict"], strict=True)
+    opt = torch.optim.AdamW(ref.parameters(), lr=1e-2)
+    opt.load_state_dict(ck["optimizer_state_dict"])
+    n_params = len(list(ref.parameters()))
+    assert len(ck["optimizer_state_dict"]["state"]) == n_params == 2 + 2 * (3 * 4 + 8) + 4
+    st = ck["optimizer_state_dict"]["state"][2 + 2]              # first head's key.weight of block 0
+    assert st["exp_avg"].shape == (16, 64)
+    # resume continues from the saved step
+    cfg2 = dict(cfg, resume_from=cfg["t_out_path"], t_train_steps=8)
+    tr2 = Trainer(Transformer(**model_args(cfg)), it, None, None, config=cfg2)
+    tr2.train()
+    assert tr2.step == 8
+
+
+def test_trainer_matches_reference_recipe(ref_models, tmp_path):
+    """Same init, same batches, AdamW defaults: our CPU trainer tracks the reference recipe."""
+    cfg = _cpu_cfg(tmp_path, t_train_steps=5, t_eval_steps=10 ** 6)
+    torch.manual_seed(3)
+    ours = Transformer(**model_args(cfg))
+    ref = ref_models.Transformer(4, 64, 32, 101, 2)
+    ref.load_state_dict(ours.state_dict())
+    batches = [next(get_batch_iterator("synthetic:101", 4, 32, seed=s)) for s in range(5)]
+    tr = Trainer(ours, iter(batches), None, None, config=cfg)
+    opt = torch.optim.AdamW(ref.parameters(), lr=cfg["t_lr"])
+    for step, (x, y) in enumerate(batches):
+        lr = get_lr(step, cfg)
+        lo = tr._train_step(x, y, lr)
+        for g in opt.param_groups:
+            g["lr"] = lr
+        _, lr_loss = ref(x, y)
+        lr_loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        assert abs(float(lo.detach()) - float(lr_loss.detach())) < 1e-4, step
+    sd, rsd = ours.state_dict(), ref.state_dict()
+    for k in rsd:
+        assert torch.allclose(sd[k].float(), rsd[k].float(), atol=1e-5), k
+
+
+def test_grad_accumulation_equals_big_batch(tmp_path):
+    cfg = _cpu_cfg(tmp_path, grad_accum_steps=2)
+    torch.manual_seed(1)
+    a = Transformer(**model_args(cfg))
+    b = Transformer(**model_args(cfg))
+    b.load_state_dict(a.state_dict())
+    x1, y1 = next(get_batch_iterator("synthetic:101", 4, 32, seed=1))
+    x2, y2 = next(get_batch_iterator("synthetic:101", 4, 32, seed=2))
+    Trainer(a, iter([(x2, y2)]), None, None, config=cfg)._train_step(x1, y1, 1e-2)
+    cfg1 = dict(cfg, grad_accum_steps=1)
+    Trainer(b, iter([]), None, None, config=cfg1)._train_step(torch.cat([x1, x2]), torch.cat([y1, y2]), 1e-2)
+    for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
+        # step-1 AdamW is ~ lr * g / (|g| + eps): only near-zero gradients may differ visibly
+        assert (p - q).abs().max() < 1e-2 * 0.05 and ((p - q).abs() > 2e-6).float().mean() < 1e-3, n
