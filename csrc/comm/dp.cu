@@ -1,0 +1,203 @@
+// Data-parallel communication over NVLink 5 / NVSwitch without NCCL on the gradient path.
+//
+//  * symmetric memory bootstrap: device buffers allocated with cudaMalloc, exported as CUDA IPC
+//    handles, imported (peer-mapped) by every other rank of the node - 64-byte handles travel
+//    over the torch.distributed store, nothing else does;
+//  * dp_reduce_adamw: ONE kernel per gradient bucket that (1) handshakes with the peers through
+//    system-scope flags in peer memory, (2) pulls this rank's 1/W slice of the bucket's fp32
+//    gradients straight out of every peer's gradient buffer (P2P loads over NVLink), sums and
+//    scales them, (3) runs the AdamW update on the slice's fp32 master weights and (sharded)
+//    moments, (4) pushes the new bf16 shadow weights (and, for parameters that are consumed in
+//    fp32 - embeddings, LayerNorm, biases - the fp32 values) into every peer's buffers (P2P
+//    stores), (5) publishes a completion flag.  It runs on a side stream as soon as backward has
+//    produced the bucket, overlapping the rest of backward.
+//  * dp_wait_done: the next forward's gate - waits until every owner has delivered every bucket.
+//
+// Replaces torch DDP's Reducer + ncclAllReduce per 25 MiB bucket + a separate foreach AdamW
+// (reference scripts/train_transformer.py:122-123,92).
+#include "b200llm.h"
+#include "common.cuh"
+
+#define DP_MAX_WORLD 8
+#define DP_MAX_SLOTS 16
+
+// ---------------------------------------------------------------------------------------------
+// symmetric memory bootstrap (CUDA IPC)
+// ---------------------------------------------------------------------------------------------
+extern "C" int b200_ipc_alloc(void** ptr, long long bytes) {
+    B200_CHECK_CUDA(cudaMalloc(ptr, (size_t)bytes));
+    B200_CHECK_CUDA(cudaMemset(*ptr, 0, (size_t)bytes));
+    return 0;
+}
+extern "C" int b200_ipc_free(void* ptr) {
+    B200_CHECK_CUDA(cudaFree(ptr));
+    return 0;
+}
+// handle_out: 64 bytes (host)
+extern "C" int b200_ipc_export(void* ptr, void* h_handle_out) {
+    cudaIpcMemHandle_t h;
+    B200_CHECK_CUDA(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(h_handle_out, &h, sizeof(h));
+    return 0;
+}
+extern "C" int b200_ipc_import(const void* h_handle, void** ptr_out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, h_handle, sizeof(h));
+    B200_CHECK_CUDA(cudaIpcOpenMemHandle(ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int b200_ipc_close(void* ptr) {
+    B200_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// flags
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// spin until *p >= target; gives up after ~20 s and raises the error flag instead of hanging
+__device__ __forceinline__ bool wait_flag(const int* p, int target, int* err) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys(p) < target) {
+        __nanosleep(64);
+        if (clock64() - t0 > 40000000000ll) {
+            if (err) *err = 1;
+            return false;
+        }
+    }
+    return true;
+}
+
+struct DpPeers {
+    float* grad[DP_MAX_WORLD];   // full flat fp32 gradient buffer of every rank
+    bf16* wb[DP_MAX_WORLD];      // full flat bf16 shadow weights of every rank
+    float* flat[DP_MAX_WORLD];   // full flat fp32 master weights of every rank
+    int* sig[DP_MAX_WORLD];      // signal pad of every rank: [2][W][NB] ints (ready | done)
+};
+struct DpSlots {                 // slots of the bucket: element END offsets (ascending) + "peers need fp32"
+    long long end[DP_MAX_SLOTS];
+    int fp32[DP_MAX_SLOTS];
+    int n;
+};
+
+template <int W>
+__global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int rank, int bucket, int nb, int epoch,
+                                                              long long start, long long n, float* __restrict__ m,
+                                                              float* __restrict__ v, const float* __restrict__ hyper,
+                                                              DpSlots slots, unsigned int* cta_counter, int* err) {
+    // ---- 1. handshake: every rank has finished writing this bucket's gradients
+    if (threadIdx.x == 0) {
+        if (blockIdx.x == 0) {
+            __threadfence_system();
+            for (int r = 0; r < W; ++r) st_release_sys(P.sig[r] + rank * nb + bucket, epoch);
+        }
+        for (int r = 0; r < W; ++r) wait_flag(P.sig[rank] + r * nb + bucket, epoch, err);
+    }
+    __syncthreads();
+
+    const float decay = hyper[0], b2 = hyper[1], w1 = hyper[2], w2 = hyper[3], step_size = hyper[4],
+                bc2s = hyper[5], eps = hyper[6], gs = hyper[7];
+    float* p_master = P.flat[rank];
+    const long long n4 = n >> 2;  // slices are multiples of 4 elements
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long e = start + i * 4;
+        // ---- 2. pull + reduce (all W loads in flight before the first add)
+        float4 g[W];
+#pragma unroll
+        for (int r = 0; r < W; ++r) g[r] = ldg_stream_f4(reinterpret_cast<const float4*>(P.grad[r] + e));
+        float4 s = g[0];
+#pragma unroll
+        for (int r = 1; r < W; ++r) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+        // ---- 3. AdamW on the owned slice (same operation order as adamw.cu)
+        float4 pv = *reinterpret_cast<float4*>(p_master + e);
+        float4 mv = reinterpret_cast<float4*>(m)[i];
+        float4 vv = reinterpret_cast<float4*>(v)[i];
+        float* pe = &pv.x; float* me = &mv.x; float* ve = &vv.x; const float* se = &s.x;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float gk = se[k] * gs;
+            pe[k] = pe[k] * decay;
+            me[k] = fmaf(w1, gk - me[k], me[k]);
+            ve[k] = fmaf(w2 * gk, gk, ve[k] * b2);
+            const float denom = __fdiv_rn(__fsqrt_rn(ve[k]), bc2s) + eps;
+            pe[k] = fmaf(-step_size, __fdiv_rn(me[k], denom), pe[k]);
+        }
+        reinterpret_cast<float4*>(m)[i] = mv;
+        reinterpret_cast<float4*>(v)[i] = vv;
+        // ---- 4. push to every rank (own copy included)
+        int need32 = 0;
+#pragma unroll 4
+        for (int k = 0; k < slots.n; ++k) {
+            if (e < slots.end[k]) { need32 = slots.fp32[k]; break; }
+        }
+        const uint2 pb = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+        *reinterpret_cast<float4*>(p_master + e) = pv;
+#pragma unroll
+        for (int r = 0; r < W; ++r) {
+            *reinterpret_cast<uint2*>(P.wb[r] + e) = pb;
+            if (need32 && r != rank) *reinterpret_cast<float4*>(P.flat[r] + e) = pv;
+        }
+    }
+    // ---- 5. publish: all CTAs' stores are visible before the done flag goes up
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int prev = atomicAdd(cta_counter, 1u);
+        if (prev == gridDim.x - 1) {
+            *cta_counter = 0;
+            __threadfence_system();
+            for (int r = 0; r < W; ++r) st_release_sys(P.sig[r] + (W + rank) * nb + bucket, epoch);
+        }
+    }
+}
+
+__global__ void dp_wait_done_kernel(const int* sig, int W, int nb, int epoch, int* err) {
+    const int i = threadIdx.x;
+    if (i < W * nb) wait_flag(sig + W * nb + i, epoch, err);
+}
+
+extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig,
+                                    int world, int rank, int bucket, int num_buckets, int epoch, long long start,
+                                    long long n, float* m, float* v, const float* hyper, const long long* h_slot_end,
+                                    const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas,
+                                    cudaStream_t st) {
+    B200_REQUIRE(world >= 1 && world <= DP_MAX_WORLD, "dp: world size %d not supported (max %d)", world, DP_MAX_WORLD);
+    B200_REQUIRE(n_slots <= DP_MAX_SLOTS, "dp: too many slots in one bucket");
+    B200_REQUIRE(n % 4 == 0 && start % 4 == 0, "dp: slice must be 16-byte aligned");
+    if (n <= 0) ctas = 1;
+    DpPeers P;
+    memset(&P, 0, sizeof(P));
+    for (int r = 0; r < world; ++r) {
+        P.grad[r] = (float*)h_grad[r]; P.wb[r] = (bf16*)h_wb[r]; P.flat[r] = (float*)h_flat[r]; P.sig[r] = (int*)h_sig[r];
+    }
+    DpSlots S;
+    memset(&S, 0, sizeof(S));
+    S.n = n_slots;
+    for (int k = 0; k < n_slots; ++k) { S.end[k] = h_slot_end[k]; S.fp32[k] = h_slot_fp32[k]; }
+#define DP_LAUNCH(W_)                                                                                            \
+    dp_reduce_adamw_kernel<W_><<<ctas, 512, 0, st>>>(P, rank, bucket, num_buckets, epoch, start, n, m, v, hyper, S, \
+                                                     (unsigned int*)cta_counter, err)
+    switch (world) {
+        case 1: DP_LAUNCH(1); break;
+        case 2: DP_LAUNCH(2); break;
+        case 4: DP_LAUNCH(4); break;
+        case 8: DP_LAUNCH(8); break;
+        default: b200_set_error("dp: world size must be 1, 2, 4 or 8"); return -1;
+    }
+#undef DP_LAUNCH
+    B200_RETURN_LAUNCH_STATUS("dp_reduce_adamw");
+}
+
+extern "C" int b200_dp_wait_done(const int* sig, int world, int num_buckets, int epoch, int* err, cudaStream_t st) {
+    B200_REQUIRE(world * num_buckets <= 1024, "dp_wait_done: too many (rank, bucket) pairs");
+    dp_wait_done_kernel<<<1, 1024, 0, st>>>(sig, world, num_buckets, epoch, err);
+    B200_RETURN_LAUNCH_STATUS("dp_wait_done");
+}

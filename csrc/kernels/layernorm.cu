@@ -171,39 +171,55 @@ __global__ void __launch_bounds__(256, 2)
                     make_uint2(pack_bf16x2(r.x, r.y), pack_bf16x2(r.z, r.w));
         }
     }
-    // partial[(cta*G + group)][NACC][d]
-    float4* pr = reinterpret_cast<float4*>(partial) + (size_t)(blockIdx.x * G + group) * NACC * D4;
+    // CTA-level reduction of the G row-groups through shared memory, then ONE partial row per CTA:
+    // partial[cta][NACC][d]
+    extern __shared__ float s_part[];   // [G][NACC][D4*4]
+    {
+        float4* sp = reinterpret_cast<float4*>(s_part) + (size_t)group * NACC * D4;
 #pragma unroll
-    for (int i = 0; i < VPL; ++i) {
-        const int c = wir * 32 + lane + i * 32 * WPR;
-        pr[c] = acc_g[i];
-        pr[D4 + c] = acc_b[i];
-        if (COLSUM) pr[2 * D4 + c] = acc_c[i];
+        for (int i = 0; i < VPL; ++i) {
+            const int c = wir * 32 + lane + i * 32 * WPR;
+            sp[c] = acc_g[i];
+            sp[D4 + c] = acc_b[i];
+            if (COLSUM) sp[2 * D4 + c] = acc_c[i];
+        }
+    }
+    __syncthreads();
+    float4* pr = reinterpret_cast<float4*>(partial) + (size_t)blockIdx.x * NACC * D4;
+    for (int e = threadIdx.x; e < NACC * D4; e += 256) {
+        float4 t = reinterpret_cast<const float4*>(s_part)[e];
+#pragma unroll
+        for (int gi = 1; gi < G; ++gi) {
+            const float4 u = reinterpret_cast<const float4*>(s_part)[(size_t)gi * NACC * D4 + e];
+            t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+        }
+        pr[e] = t;
     }
 }
 
-// out[k][c] (+)= sum_p partial[p][k][c]
-__global__ void __launch_bounds__(128) ln_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int nacc,
+// out[k][c] (+)= sum_p partial[p][k][c];  CTA = 32 columns x 8 row lanes, grid = (d/32, nacc)
+__global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int nacc,
                                                               int d, float* __restrict__ o0, float* __restrict__ o1,
                                                               float* __restrict__ o2, int accumulate) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
     const int k = blockIdx.y;
-    if (c >= d) return;
     float* o = k == 0 ? o0 : (k == 1 ? o1 : o2);
-    if (o == nullptr) return;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    const float* p = partial + (size_t)k * d + c;
-    const size_t stride = (size_t)nacc * d;
-    int i = 0;
-    for (; i + 3 < nparts; i += 4) {
-        s0 += p[(size_t)i * stride];
-        s1 += p[(size_t)(i + 1) * stride];
-        s2 += p[(size_t)(i + 2) * stride];
-        s3 += p[(size_t)(i + 3) * stride];
+    __shared__ float red[8][33];
+    float s = 0.f;
+    if (c < d && o != nullptr) {
+        const float* p = partial + (size_t)k * d + c;
+        const size_t stride = (size_t)nacc * d;
+        for (int i = ty; i < nparts; i += 8) s += p[(size_t)i * stride];
     }
-    for (; i < nparts; ++i) s0 += p[(size_t)i * stride];
-    float s = (s0 + s1) + (s2 + s3);
-    o[c] = accumulate ? o[c] + s : s;
+    red[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && c < d && o != nullptr) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t += red[j][tx];
+        o[c] = accumulate ? o[c] + t : t;
+    }
 }
 
 struct LnCfg { int vpl, wpr; };
@@ -262,7 +278,7 @@ extern "C" int b200_ln_bwd_nparts(int M, int d) {
     if (!ln_cfg(d, &cfg)) return -1;
     const int G = 8 / cfg.wpr;
     int grid = min((M + G - 1) / G, b200_num_sms() * 2);
-    return max(grid, 1) * G;
+    return max(grid, 1);
 }
 
 extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* rstd,
@@ -276,15 +292,24 @@ extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, co
     const int grid = max(1, min((M + G - 1) / G, b200_num_sms() * 2));
     const bool cs = colsum != nullptr;
     B200_REQUIRE(!cs || dx_in != nullptr, "ln_bwd: colsum needs dx_in");
-    if (cs) {
-        LN_DISPATCH_ALL((ln_bwd_kernel<VPL, WPR, true><<<grid, 256, 0, st>>>(
-            (const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M)))
-    } else {
-        LN_DISPATCH_ALL((ln_bwd_kernel<VPL, WPR, false><<<grid, 256, 0, st>>>(
-            (const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M)))
-    }
     const int nacc = cs ? 3 : 2;
-    ln_bwd_finalize_kernel<<<dim3((d + 127) / 128, nacc), 128, 0, st>>>(partial, grid * G, nacc, d, dgamma, dbeta,
-                                                                         colsum, accumulate);
+    const int smem = G * nacc * d * (int)sizeof(float);
+    if (cs) {
+        LN_DISPATCH_ALL({
+            auto kern = ln_bwd_kernel<VPL, WPR, true>;
+            static bool cfg_done = false;
+            if (!cfg_done) { B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304)); cfg_done = true; }
+            kern<<<grid, 256, smem, st>>>((const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M);
+        })
+    } else {
+        LN_DISPATCH_ALL({
+            auto kern = ln_bwd_kernel<VPL, WPR, false>;
+            static bool cfg_done = false;
+            if (!cfg_done) { B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304)); cfg_done = true; }
+            kern<<<grid, 256, smem, st>>>((const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M);
+        })
+    }
+    ln_bwd_finalize_kernel<<<dim3((d + 31) / 32, nacc), 256, 0, st>>>(partial, grid, nacc, d, dgamma, dbeta, colsum,
+                                                                       accumulate);
     B200_RETURN_LAUNCH_STATUS("ln_bwd");
 }

@@ -99,6 +99,24 @@ int b200_scatter_tokens(const long long* next, long long* seq, int B, long long 
 /* out[b, :] = in[b*T + T-1, :] : the last-position rows, for the last-token-only LM head */
 int b200_gather_last_rows(const void* in, void* out, int B, int T, int row_bytes, cudaStream_t st);
 
+/* ---- data parallel over NVLink (ref: torch DDP + AdamW, scripts/train_transformer.py:122-123,92) ----
+ * Symmetric memory bootstrap: cudaMalloc'd buffers exported / imported as 64-byte CUDA IPC handles.
+ * b200_ipc_alloc is the one allocating call of this library (set-up time, never per step). */
+int b200_ipc_alloc(void** ptr, long long bytes);
+int b200_ipc_free(void* ptr);
+int b200_ipc_export(void* ptr, void* h_handle_out);
+int b200_ipc_import(const void* h_handle, void** ptr_out);
+int b200_ipc_close(void* ptr);
+/* Fused per-bucket gradient reduce-scatter (P2P loads) + scale + AdamW on the owned 1/W slice
+ * [start, start+n) + all-gather of the updated weights (P2P stores of bf16, and fp32 where flagged).
+ * h_grad/h_wb/h_flat/h_sig: host arrays of `world` peer-mapped device pointers (own rank included);
+ * sig: int[2][world][num_buckets] per rank (ready | done), zero-initialised; epoch: 1, 2, 3, ...;
+ * m, v: this rank's moments for the slice; h_slot_end / h_slot_fp32: element end offsets and
+ * "consumers read fp32" flags of the parameter slots inside the bucket. */
+int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig, int world, int rank, int bucket, int num_buckets, int epoch, long long start, long long n, float* m, float* v, const float* hyper, const long long* h_slot_end, const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas, cudaStream_t st);
+/* blocks the stream until every owner's done flag of every bucket has reached `epoch` */
+int b200_dp_wait_done(const int* sig, int world, int num_buckets, int epoch, int* err, cudaStream_t st);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,206 @@
+"""Data parallelism with the collective fused into the optimizer kernel.
+
+What torch DDP does for the reference (``DDP(model)`` at reference
+``scripts/train_transformer.py:122-123``: bucketed fp32 ``ncclAllReduce`` from autograd hooks, then a
+separate ``foreach`` AdamW over every replica's full parameter set) is done here by ONE kernel per
+gradient bucket (``csrc/comm/dp.cu``), launched on a side stream the moment backward has finished
+the bucket:
+
+    reduce-scatter   each rank pulls its 1/W slice of the bucket from every peer's gradient
+                     buffer with P2P loads over NVLink and sums it (fp32, scaled by 1/W)
+    AdamW            on that slice only - fp32 master weights and the moments are sharded
+                     across ranks (ZeRO-1 style: optimizer state is 1/W per GPU)
+    all-gather       the new bf16 weights (fp32 too for tensors consumed in fp32: embeddings,
+                     LayerNorm, biases) are pushed into every peer's weight buffers with P2P stores
+
+Cross-rank ordering uses system-scope flags in peer-mapped signal pads; the next forward is gated by
+``b200_dp_wait_done``.  Buckets follow backward order: LM head, blocks L-1..0, embeddings.  Every
+rank launches the same kernels in the same order; spin loops time out into an error flag.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Dict, List, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..models.layout import ParamLayout
+from ..ops import lib
+from .. import ops
+
+F32, BF16 = torch.float32, torch.bfloat16
+_BF16_ONLY = ("attn.wqkv", "mlp.hidden.weight", "mlp.proj.weight", "lm_head.weight")
+
+
+@dataclass
+class BucketPlan:
+    name: str
+    start: int            # element offset of the bucket in the flat buffer
+    end: int
+    chunk: int            # elements owned by each rank (last rank may own fewer)
+    slot_end: List[int]   # ascending element END offsets of the slots in the bucket
+    slot_fp32: List[int]  # 1 if consumers read this slot in fp32 (must be pushed in fp32 too)
+
+    def slice_of(self, rank: int) -> Tuple[int, int]:
+        s = min(self.end, self.start + rank * self.chunk)
+        e = min(self.end, s + self.chunk)
+        return s, e - s
+
+
+def plan_buckets(layout: ParamLayout, world: int) -> List[BucketPlan]:
+    """Static ownership map: bucket b's elements [start + r*chunk, start + (r+1)*chunk) belong to rank r."""
+    slots = list(layout.slots.values())
+    plans = []
+    for name, start, end in layout.buckets():
+        n = end - start
+        chunk = (n + world - 1) // world
+        chunk = (chunk + 3) // 4 * 4
+        inside = [s for s in slots if start <= s.offset < end]
+        slot_end, slot_fp32 = [], []
+        for i, s in enumerate(inside):
+            nxt = inside[i + 1].offset if i + 1 < len(inside) else end
+            slot_end.append(nxt)
+            slot_fp32.append(0 if s.name.endswith(_BF16_ONLY) else 1)
+        plans.append(BucketPlan(name, start, end, chunk, slot_end, slot_fp32))
+    return plans
+
+
+class DataParallel:
+    def __init__(self, eng, ctx, mode: str = "ddp", ctas: int = 32):
+        from .symm import SymmBuffer
+        if mode not in ("ddp", "zero"):
+            raise ValueError(mode)
+        self.eng, self.ctx, self.mode, self.ctas = eng, ctx, mode, ctas
+        self.world, self.rank = ctx.world, ctx.rank
+        if self.world not in (1, 2, 4, 8):
+            raise ValueError("data-parallel world size must be 1, 2, 4 or 8 (one NVSwitch domain)")
+        lay: ParamLayout = eng.layout
+        dev = eng.device
+        n = lay.total
+        self.plans = plan_buckets(lay, self.world)
+        self.nb = len(self.plans)
+        self.index: Dict[str, int] = {p.name: i for i, p in enumerate(self.plans)}
+        # ---- symmetric buffers: gradients, bf16 weights, fp32 masters, signal pad
+        self.sym_grad = SymmBuffer(n * 4, self.rank, self.world, dev)
+        self.sym_wb = SymmBuffer(n * 2, self.rank, self.world, dev)
+        self.sym_flat = SymmBuffer(n * 4, self.rank, self.world, dev)
+        self.sym_sig = SymmBuffer(2 * self.world * self.nb * 4, self.rank, self.world, dev)
+        new_flat = self.sym_flat.view(F32)[:n]
+        new_flat.copy_(eng.flat)
+        dist.broadcast(new_flat, src=0)                   # identical replicas to start from
+        model = eng.model
+        with torch.no_grad():
+            for name, p in model.named_parameters():
+                p.data = lay.view(new_flat, name)
+        model._flat = new_flat
+        eng.flat = new_flat
+        eng.wb = self.sym_wb.view(BF16)[:n]
+        eng.grad = self.sym_grad.view(F32)[:n]
+        eng.params_changed()
+        eng.sync_weights()
+        # ---- sharded optimizer state: only the owned slices
+        self.owned = [p.slice_of(self.rank) for p in self.plans]
+        total_owned = sum(cnt for _, cnt in self.owned)
+        self.m = torch.zeros(max(total_owned, 4), device=dev, dtype=F32)
+        self.v = torch.zeros(max(total_owned, 4), device=dev, dtype=F32)
+        self.opt_off = []
+        off = 0
+        for _, cnt in self.owned:
+            self.opt_off.append(off)
+            off += cnt
+        if eng.exp_avg is not None:
+            self.state_loaded()
+        self.counter = torch.zeros(self.nb, device=dev, dtype=torch.int32)
+        self.err = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.epoch = 0
+        self.comm_stream = torch.cuda.Stream(device=dev)
+        self._launched = set()
+        self._slot_arrays = []
+        for p in self.plans:
+            k = len(p.slot_end)
+            self._slot_arrays.append(((ctypes.c_longlong * k)(*p.slot_end), (ctypes.c_int * k)(*p.slot_fp32), k))
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ per-step protocol
+    def bucket_ready(self, name: str) -> None:
+        """Called by Engine.backward right after the bucket's last gradient kernel was enqueued."""
+        b = self.index[name]
+        if b == 0:
+            self.epoch += 1
+            self._launched = set()
+        main = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self.comm_stream.wait_event(ev)
+        self._launch(b)
+
+    def _launch(self, b: int) -> None:
+        start, cnt = self.owned[b]
+        end_arr, fp_arr, k = self._slot_arrays[b]
+        off = self.opt_off[b]
+        L = lib.load()
+        rc = L.b200_dp_reduce_adamw(self.sym_grad.ptr_array, self.sym_wb.ptr_array, self.sym_flat.ptr_array,
+                                    self.sym_sig.ptr_array, self.world, self.rank, b, self.nb, self.epoch, start, cnt,
+                                    self.m[off:].data_ptr(), self.v[off:].data_ptr(), self.eng.hyper.data_ptr(),
+                                    end_arr, fp_arr, k, self.counter[b:].data_ptr(), self.err.data_ptr(),
+                                    self.ctas, self.comm_stream.cuda_stream)
+        lib.check(rc, "dp_reduce_adamw")
+        ops.LAUNCHES += 1
+        self._launched.add(b)
+
+    def reduce_and_step(self) -> None:
+        """End of the step: reduce whatever has not been launched yet (the embedding bucket), then gate
+        the main stream on every owner having delivered every bucket."""
+        main = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self.comm_stream.wait_event(ev)
+        if 0 not in self._launched:                      # backward did not call the hooks (e.g. accumulate path)
+            self.epoch += 1
+            self._launched = set()
+        for b in range(self.nb):
+            if b not in self._launched:
+                self._launch(b)
+        done = torch.cuda.Event()
+        done.record(self.comm_stream)
+        main.wait_event(done)
+        rc = lib.load().b200_dp_wait_done(self.sym_sig.view(torch.int32).data_ptr(), self.world, self.nb, self.epoch,
+                                          self.err.data_ptr(), main.cuda_stream)
+        lib.check(rc, "dp_wait_done")
+        ops.LAUNCHES += 1
+
+    def check_errors(self) -> None:
+        if int(self.err.item()) != 0:
+            raise RuntimeError("data-parallel kernel timed out waiting for a peer (a rank died or diverged)")
+
+    # ------------------------------------------------------------------ full state for checkpoints
+    def _gather(self, local_slices: List[torch.Tensor], out_flat: torch.Tensor) -> None:
+        for p, loc in zip(self.plans, local_slices):
+            pad = torch.zeros(p.chunk, device=loc.device, dtype=loc.dtype)
+            pad[:loc.numel()] = loc
+            parts = [torch.empty_like(pad) for _ in range(self.world)]
+            dist.all_gather(parts, pad)
+            for r, part in enumerate(parts):
+                s, cnt = p.slice_of(r)
+                out_flat[s:s + cnt] = part[:cnt]
+
+    def gather_full_state(self) -> None:
+        """Make fp32 masters complete on every rank and materialise full moments in eng.exp_avg(_sq).
+        Collective: every rank must call it."""
+        eng = self.eng
+        torch.cuda.synchronize()
+        self._gather([eng.flat[s:s + c] for s, c in self.owned], eng.flat)
+        eng.ensure_opt_state()
+        self._gather([self.m[o:o + c] for o, (_, c) in zip(self.opt_off, self.owned)], eng.exp_avg)
+        self._gather([self.v[o:o + c] for o, (_, c) in zip(self.opt_off, self.owned)], eng.exp_avg_sq)
+        eng._wb_version = eng.flat._version
+
+    def state_loaded(self) -> None:
+        """Full moments were loaded into eng.exp_avg(_sq) (resume): keep the owned slices."""
+        eng = self.eng
+        for o, (s, c) in zip(self.opt_off, self.owned):
+            self.m[o:o + c] = eng.exp_avg[s:s + c]
+            self.v[o:o + c] = eng.exp_avg_sq[s:s + c]

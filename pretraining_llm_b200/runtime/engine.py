@@ -96,7 +96,6 @@ class Engine:
         self.exp_avg_sq: Optional[torch.Tensor] = None
         self.step_count = 0
         self.hyper = torch.zeros(8, device=self.device, dtype=F32)
-        self.hyper_host = torch.zeros(8, dtype=F32).pin_memory()
         self.betas, self.eps, self.weight_decay = (0.9, 0.999), 1e-8, 0.01   # torch.optim.AdamW defaults
         self.ws: Dict[Tuple[int, int, bool], Workspace] = {}
         self.dp = None                     # parallel.dp.DataParallel, set by attach_dp()
@@ -204,8 +203,13 @@ class Engine:
                             sum_scale=loss_scale / w.M)
 
     # ------------------------------------------------------------------ backward
-    def backward(self, w: Workspace, *, grad_scale: float = 1.0, accumulate: bool = False) -> None:
-        """Gradients of (grad_scale * mean CE) w.r.t. every parameter -> the flat fp32 grad buffer."""
+    def backward(self, w: Workspace, *, grad_scale: float = 1.0, accumulate: bool = False,
+                 dp_sync: bool = True) -> None:
+        """Gradients of (grad_scale * mean CE) w.r.t. every parameter -> the flat fp32 grad buffer.
+        With data parallelism attached, each finished bucket is handed to the fused
+        reduce+AdamW kernel on the communication stream (``dp_sync=False`` on all but the last
+        micro-step of a gradient accumulation)."""
+        dp = self.dp if dp_sync else None
         assert w.train, "backward needs a training workspace"
         self.ensure_grad()
         lay = self.layout
@@ -221,6 +225,8 @@ class Engine:
         stf = w.ln_stats[2 * L]
         ops.ln_bwd(w.dtmp, w.resid_a[L], stf[0], stf[1], self.P("layer_norm.weight"), self.G("layer_norm.weight"),
                    self.G("layer_norm.bias"), dx_out=w.dx, dx_bf16=w.dx_bf16, partial=w.ln_partial, accumulate=accumulate)
+        if dp is not None:
+            dp.bucket_ready("head")
         for l in reversed(range(L)):
             pre = f"attn_blocks.{l}."
             st1, st2 = w.ln_stats[2 * l], w.ln_stats[2 * l + 1]
@@ -241,8 +247,8 @@ class Engine:
             ops.ln_bwd(w.dtmp, w.resid_a[l], st1[0], st1[1], self.P(pre + "ln1.weight"), self.G(pre + "ln1.weight"),
                        self.G(pre + "ln1.bias"), dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16, partial=w.ln_partial,
                        accumulate=accumulate)
-            if self.dp is not None:
-                self.dp.bucket_ready(l)
+            if dp is not None:
+                dp.bucket_ready(f"block{l}")
         ops.embed_bwd(w.idx, w.dx, self.G("token_embed.weight"), self.G("position_embed.weight")[:T],
                       accumulate=accumulate)
         if not accumulate and T < lay.ctx:
@@ -252,10 +258,12 @@ class Engine:
     def set_hyper(self, lr: float, grad_scale: float = 1.0) -> None:
         """Stage AdamW scalars for the NEXT optimizer launch (also read by graph replays)."""
         self.step_count += 1
+        if self.dp is not None:
+            grad_scale = grad_scale / self.dp.world       # average of the per-rank mean losses
         vals = ops.adamw_hyper(lr, self.step_count, self.betas[0], self.betas[1], self.eps, self.weight_decay,
                                grad_scale)
-        self.hyper_host.copy_(torch.tensor(vals, dtype=F32))
-        self.hyper.copy_(self.hyper_host, non_blocking=True)
+        # pageable source: the driver stages the 32 bytes at call time, so later host writes cannot race
+        self.hyper.copy_(torch.tensor(vals, dtype=F32))
         self.lr = lr
 
     def optimizer_step(self) -> None:

@@ -99,7 +99,7 @@ class Trainer:
                 if k:
                     xb, yb = next(self.train_iterator)
                 w, _, loss = eng.forward(xb.contiguous(), yb.contiguous(), train=True)
-                eng.backward(w, grad_scale=1.0 / accum, accumulate=k > 0)
+                eng.backward(w, grad_scale=1.0 / accum, accumulate=k > 0, dp_sync=(k == accum - 1))
                 loss_acc = loss.clone() if loss_acc is None else loss_acc + loss
             eng.set_hyper(lr)
             eng.optimizer_step()

@@ -1,0 +1,21 @@
+"""GPU tier, multi-GPU: the fused gradient reduce + AdamW + weight broadcast kernel over NVLink.
+Needs >= 2 GPUs on the box (skipped on a single-GPU box; the CPU tier covers the host logic)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_fused_dp_matches_single_gpu(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(29700 + world),
+                        os.path.join(ROOT, "tools", "dp_check.py")], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "DP_CHECK_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

@@ -91,7 +91,9 @@ def test_train_steps_track_torch_adamw():
     assert native.engine.workspace(4, 128, True).graph is not None
     # parameters stay close after 8 optimizer steps
     for (n, p), (_, q) in zip(native.named_parameters(), oracle.named_parameters()):
-        assert (p - q).abs().max() < 8e-3, n                 # 8 steps * lr 1e-3 bounds the drift
+        diff = (p - q).abs()
+        assert diff.max() < 2e-2, n                           # 8 steps * lr 1e-3, opposite signs at worst
+        assert diff.mean() < 4e-4, (n, diff.mean().item())
 
 
 def test_overfit_one_batch_and_checkpoint_roundtrip(tmp_path, ref_models):
