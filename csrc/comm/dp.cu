@@ -88,10 +88,11 @@ struct DpSlots {                 // slots of the bucket: element END offsets (as
 };
 
 template <int W>
-__global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int rank, int bucket, int nb, int epoch,
+__global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int rank, int bucket, int nb, const int* __restrict__ epoch_dev,
                                                               long long start, long long n, float* __restrict__ m,
                                                               float* __restrict__ v, const float* __restrict__ hyper,
                                                               DpSlots slots, unsigned int* cta_counter, int* err) {
+    const int epoch = *epoch_dev;   // device-resident step counter: the same CUDA graph serves every step
     // ---- 1. handshake: every rank has finished writing this bucket's gradients
     if (threadIdx.x == 0) {
         if (blockIdx.x == 0) {
@@ -159,13 +160,14 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
     }
 }
 
-__global__ void dp_wait_done_kernel(const int* sig, int W, int nb, int epoch, int* err) {
+__global__ void dp_wait_done_kernel(const int* sig, int W, int nb, const int* epoch_dev, int* err) {
+    const int epoch = *epoch_dev;
     const int i = threadIdx.x;
     if (i < W * nb) wait_flag(sig + W * nb + i, epoch, err);
 }
 
 extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig,
-                                    int world, int rank, int bucket, int num_buckets, int epoch, long long start,
+                                    int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start,
                                     long long n, float* m, float* v, const float* hyper, const long long* h_slot_end,
                                     const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas,
                                     cudaStream_t st) {
@@ -183,7 +185,7 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
     S.n = n_slots;
     for (int k = 0; k < n_slots; ++k) { S.end[k] = h_slot_end[k]; S.fp32[k] = h_slot_fp32[k]; }
 #define DP_LAUNCH(W_)                                                                                            \
-    dp_reduce_adamw_kernel<W_><<<ctas, 512, 0, st>>>(P, rank, bucket, num_buckets, epoch, start, n, m, v, hyper, S, \
+    dp_reduce_adamw_kernel<W_><<<ctas, 512, 0, st>>>(P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
                                                      (unsigned int*)cta_counter, err)
     switch (world) {
         case 1: DP_LAUNCH(1); break;
@@ -196,8 +198,9 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
     B200_RETURN_LAUNCH_STATUS("dp_reduce_adamw");
 }
 
-extern "C" int b200_dp_wait_done(const int* sig, int world, int num_buckets, int epoch, int* err, cudaStream_t st) {
+extern "C" int b200_dp_wait_done(const int* sig, int world, int num_buckets, const int* epoch_dev, int* err,
+                                 cudaStream_t st) {
     B200_REQUIRE(world * num_buckets <= 1024, "dp_wait_done: too many (rank, bucket) pairs");
-    dp_wait_done_kernel<<<1, 1024, 0, st>>>(sig, world, num_buckets, epoch, err);
+    dp_wait_done_kernel<<<1, 1024, 0, st>>>(sig, world, num_buckets, epoch_dev, err);
     B200_RETURN_LAUNCH_STATUS("dp_wait_done");
 }

@@ -110,12 +110,13 @@ int b200_ipc_close(void* ptr);
 /* Fused per-bucket gradient reduce-scatter (P2P loads) + scale + AdamW on the owned 1/W slice
  * [start, start+n) + all-gather of the updated weights (P2P stores of bf16, and fp32 where flagged).
  * h_grad/h_wb/h_flat/h_sig: host arrays of `world` peer-mapped device pointers (own rank included);
- * sig: int[2][world][num_buckets] per rank (ready | done), zero-initialised; epoch: 1, 2, 3, ...;
+ * sig: int[2][world][num_buckets] per rank (ready | done), zero-initialised; *epoch_dev: 1, 2, 3, ...
+ * (a device int the caller increments once per step, so a captured graph can be replayed);
  * m, v: this rank's moments for the slice; h_slot_end / h_slot_fp32: element end offsets and
  * "consumers read fp32" flags of the parameter slots inside the bucket. */
-int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig, int world, int rank, int bucket, int num_buckets, int epoch, long long start, long long n, float* m, float* v, const float* hyper, const long long* h_slot_end, const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas, cudaStream_t st);
+int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start, long long n, float* m, float* v, const float* hyper, const long long* h_slot_end, const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas, cudaStream_t st);
 /* blocks the stream until every owner's done flag of every bucket has reached `epoch` */
-int b200_dp_wait_done(const int* sig, int world, int num_buckets, int epoch, int* err, cudaStream_t st);
+int b200_dp_wait_done(const int* sig, int world, int num_buckets, const int* epoch_dev, int* err, cudaStream_t st);
 
 #ifdef __cplusplus
 }

@@ -114,7 +114,7 @@ class DataParallel:
             self.state_loaded()
         self.counter = torch.zeros(self.nb, device=dev, dtype=torch.int32)
         self.err = torch.zeros(1, device=dev, dtype=torch.int32)
-        self.epoch = 0
+        self.epoch_dev = torch.zeros(1, device=dev, dtype=torch.int32)   # incremented on the device each step
         self.comm_stream = torch.cuda.Stream(device=dev)
         self._launched = set()
         self._slot_arrays = []
@@ -128,9 +128,6 @@ class DataParallel:
     def bucket_ready(self, name: str) -> None:
         """Called by Engine.backward right after the bucket's last gradient kernel was enqueued."""
         b = self.index[name]
-        if b == 0:
-            self.epoch += 1
-            self._launched = set()
         main = torch.cuda.current_stream()
         ev = torch.cuda.Event()
         ev.record(main)
@@ -143,7 +140,7 @@ class DataParallel:
         off = self.opt_off[b]
         L = lib.load()
         rc = L.b200_dp_reduce_adamw(self.sym_grad.ptr_array, self.sym_wb.ptr_array, self.sym_flat.ptr_array,
-                                    self.sym_sig.ptr_array, self.world, self.rank, b, self.nb, self.epoch, start, cnt,
+                                    self.sym_sig.ptr_array, self.world, self.rank, b, self.nb, self.epoch_dev.data_ptr(), start, cnt,
                                     self.m[off:].data_ptr(), self.v[off:].data_ptr(), self.eng.hyper.data_ptr(),
                                     end_arr, fp_arr, k, self.counter[b:].data_ptr(), self.err.data_ptr(),
                                     self.ctas, self.comm_stream.cuda_stream)
@@ -158,19 +155,22 @@ class DataParallel:
         ev = torch.cuda.Event()
         ev.record(main)
         self.comm_stream.wait_event(ev)
-        if 0 not in self._launched:                      # backward did not call the hooks (e.g. accumulate path)
-            self.epoch += 1
-            self._launched = set()
         for b in range(self.nb):
             if b not in self._launched:
                 self._launch(b)
         done = torch.cuda.Event()
         done.record(self.comm_stream)
         main.wait_event(done)
-        rc = lib.load().b200_dp_wait_done(self.sym_sig.view(torch.int32).data_ptr(), self.world, self.nb, self.epoch,
-                                          self.err.data_ptr(), main.cuda_stream)
+        rc = lib.load().b200_dp_wait_done(self.sym_sig.view(torch.int32).data_ptr(), self.world, self.nb,
+                                          self.epoch_dev.data_ptr(), self.err.data_ptr(), main.cuda_stream)
         lib.check(rc, "dp_wait_done")
         ops.LAUNCHES += 1
+        self._launched = set()
+
+    def begin_step(self) -> None:
+        """First thing of a step (main stream): advance the device-side epoch."""
+        ops.incr_int(self.epoch_dev, 1)
+        self._launched = set()
 
     def check_errors(self) -> None:
         if int(self.err.item()) != 0:

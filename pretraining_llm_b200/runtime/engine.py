@@ -296,7 +296,7 @@ class Engine:
         self.set_hyper(lr)
         if use_graph and w.graph is not None:
             w.graph.replay()
-        elif use_graph and getattr(w, "warm", False) and self.dp is None:
+        elif use_graph and getattr(w, "warm", False):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self._step_body(w)
@@ -308,6 +308,8 @@ class Engine:
         return w.loss[0]
 
     def _step_body(self, w: Workspace) -> None:
+        if self.dp is not None:
+            self.dp.begin_step()
         self._forward_ws(w, True)
         self.backward(w)
         self.optimizer_step()

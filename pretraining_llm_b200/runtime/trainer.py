@@ -95,6 +95,8 @@ class Trainer:
             if accum == 1:
                 return eng.train_step(xb, yb, lr, use_graph=self.config.get("use_cuda_graph", True))
             loss_acc = None
+            if eng.dp is not None:
+                eng.dp.begin_step()
             for k in range(accum):
                 if k:
                     xb, yb = next(self.train_iterator)

@@ -51,7 +51,7 @@ def main():
     dist.all_reduce(mean_loss)
     mean_loss /= W
     # (2) bf16 replicas identical
-    wb = eng.wb.view(torch.int16).clone()
+    wb = eng.wb.clone()
     ref = wb.clone()
     dist.broadcast(ref, src=0)
     same = torch.equal(wb, ref)
