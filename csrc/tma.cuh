@@ -85,4 +85,43 @@ inline int make_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t co
     return 0;
 }
 
+// 3-D tensor [d2][d1][d0] (d0 contiguous), pitches in bytes for d1 and d2, box = {b0, b1, 1}, 128-byte swizzle.
+// Used for per-batch attention tiles: out-of-range rows of one batch element are zero-filled on load and
+// clipped on store instead of spilling into the next batch element.
+inline int make_3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t pitch1,
+                   uint64_t pitch2, uint32_t b0, uint32_t b1, uint32_t elt) {
+    static std::mutex mu;
+    static std::unordered_map<Key, CUtensorMap, KeyHash> cache;
+    Key k;
+    memset(&k, 0, sizeof(k));
+    k.ptr = ptr; k.d0 = d0; k.d1 = d1 ^ (d2 << 40); k.ld_bytes = pitch1 ^ (pitch2 << 1); k.b0 = b0; k.b1 = b1; k.elt = elt;
+    k.swz = 3;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = cache.find(k);
+        if (it != cache.end()) { *out = it->second; return 0; }
+    }
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) { b200_set_error("cuTensorMapEncodeTiled entry point not available"); return -1; }
+    if ((uintptr_t)ptr % 16 != 0 || pitch1 % 16 != 0 || pitch2 % 16 != 0) {
+        b200_set_error("TMA: base pointer and pitches must be 16-byte aligned");
+        return -1;
+    }
+    cuuint64_t dims[3] = {d0, d1, d2};
+    cuuint64_t strides[2] = {pitch1, pitch2};
+    cuuint32_t box[3] = {b0, b1, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUtensorMapDataType dt = elt == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    CUresult r = fn(out, dt, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        b200_set_error("cuTensorMapEncodeTiled(3d) failed: CUresult %d", (int)r);
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    if (cache.size() > 65536) cache.clear();
+    cache.emplace(k, *out);
+    return 0;
+}
+
 }  // namespace tma

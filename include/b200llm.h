@@ -78,6 +78,8 @@ int b200_ce_grad(void* logits, long long ld, const float* lse, const long long* 
  * qkv [B*T, 3*H*hs] bf16 (q | k | v thirds, head h at columns h*hs); out [B*T, H*hs] bf16
  * head-major (the reference's torch.cat of heads); lse [B, H, T] fp32. hs in {64, 128}. */
 int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale, cudaStream_t st);
+/* same contract on tcgen05/TMEM/TMA (S and O accumulate in tensor memory; the default forward) */
+int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale, cudaStream_t st);
 /* dqkv [B*T, 3*H*hs] bf16; delta [B, H, T] fp32 scratch; dq_acc [B*T, H*hs] fp32 scratch */
 int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t st);
 

@@ -8,6 +8,7 @@ allocated with torch.
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional
 
 import torch
@@ -170,12 +171,17 @@ def ce_grad(logits, lse, targets, dbias, V, scale: float, accumulate: bool = Fal
 
 
 # ------------------------------------------------------------------------------------------ attention
-def attn_fwd(qkv, B, T, H, hs, out=None, lse=None):
+ATTN_FWD_IMPL = os.environ.get("B200_ATTN_FWD", "tc")   # "tc" = tcgen05/TMEM kernel, "mma" = mma.sync kernel
+
+
+def attn_fwd(qkv, B, T, H, hs, out=None, lse=None, impl: Optional[str] = None):
     if out is None:
         out = torch.empty(B * T, H * hs, device=qkv.device, dtype=BF16)
     if lse is None:
         lse = torch.empty(B, H, T, device=qkv.device, dtype=F32)
-    _chk(lib.load().b200_attn_fwd(_p(qkv), _p(out), _p(lse), B, T, H, hs, 1.0 / math.sqrt(hs), _st()), "attn_fwd")
+    L = lib.load()
+    fn = L.b200_attn_fwd_tc if (impl or ATTN_FWD_IMPL) == "tc" else L.b200_attn_fwd
+    _chk(fn(_p(qkv), _p(out), _p(lse), B, T, H, hs, 1.0 / math.sqrt(hs), _st()), "attn_fwd")
     return out, lse
 
 

@@ -199,13 +199,14 @@ def _ref_attn(qkv, B, T, H, hs):
     return o.transpose(1, 2).reshape(B * T, H * hs)
 
 
+@pytest.mark.parametrize("impl", ["tc", "mma"])
 @pytest.mark.parametrize("hs", [64, 128])
 @pytest.mark.parametrize("T", [1, 17, 128, 200, 1024])
-def test_flash_attention_fwd_bwd(ops, hs, T):
+def test_flash_attention_fwd_bwd(ops, hs, T, impl):
     torch.manual_seed(8)
     B, H = 2, 3
     qkv = _rand(B * T, 3 * H * hs)
-    out, lse = ops.attn_fwd(qkv, B, T, H, hs)
+    out, lse = ops.attn_fwd(qkv, B, T, H, hs, impl=impl)
     qr = qkv.float().requires_grad_(True)
     ref = _ref_attn(qr, B, T, H, hs)
     assert _rel(out, ref) < 8e-3, _rel(out, ref)
