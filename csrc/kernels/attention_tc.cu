@@ -302,6 +302,356 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, floa
     return 0;
 }
 
+
+// =============================================================================================
+// Backward on tcgen05: two passes of ONE kernel template, no atomics, no fp32 scratch.
+//
+//   pass DKV (key-stationary):   CTA = 128 keys of one (b, h); streams 64-query tiles i >= diagonal
+//        S^T = K Q_i^T , dP^T = V dO_i^T                    2 MMAs (M=128 keys, N=64 queries) -> TMEM
+//        P^T = exp2(S^T c - lse[q]) , dS^T = P^T (dP^T - delta[q]) scale      thread = key row
+//        dV += P^T dO_i , dK += dS^T Q_i                    2 MMAs accumulate in TMEM over all i
+//   pass DQ (query-stationary):  CTA = 128 queries; streams 64-key tiles j <= diagonal
+//        S = Q K_j^T , dP = dO V_j^T                        2 MMAs (M=128 queries, N=64 keys)
+//        dS = P (dP - delta[q]) scale                       thread = query row
+//        dQ += dS K_j                                       1 MMA accumulates in TMEM over all j
+//
+// Both passes have the same shape: two "score" MMAs [128 x 64] with K = hs from K-major smem tiles,
+// an elementwise stage that writes bf16 tiles [128 x 64] to swizzled smem, and "accumulate" MMAs
+// [128 x hs] with K = 64 whose B operand is the streamed tile read MN-major.  Recomputing S in the
+// second pass costs 2 extra MMAs per tile pair but removes the cross-CTA dQ reduction entirely
+// (fp32 RED traffic + a conversion pass were the bottleneck of the single-pass version).
+// hs=64: 256 TMEM columns and < 113 KB smem per CTA, so two CTAs share an SM and overlap each
+// other's MMA / exponential phases.
+// Warp roles: 0 TMA, 1 MMA, 2-5 elementwise + epilogue.
+// =============================================================================================
+constexpr int SUB64 = 64 * 64 * 2;     // [64 rows x 64 cols] bf16 sub-tile = 8 KiB
+
+template <int HD, bool DKV> struct BCfg {
+    static constexpr int NSUB = HD / 64;
+    static constexpr int STAT = NSUB * SUB;                 // stationary tile [128 x HD]
+    static constexpr int STR = NSUB * SUB64;                // streamed tile  [64 x HD]
+    static constexpr int NOUT = DKV ? 2 : 1;                // bf16 tiles produced per iteration (P^T, dS^T | dS)
+    static constexpr int NACC = DKV ? 2 : 1;                // TMEM accumulators (dV, dK | dQ)
+    static constexpr int SC1 = 0, SC2 = 64, ACC = 128;      // TMEM columns
+    static constexpr int TMEM_COLS = (128 + NACC * HD) <= 256 ? 256 : 512;
+    static constexpr int USED = 2 * STAT + 2 * 2 * STR + NOUT * SUB + 1280;   // stat x2 | streamed x2 stages x2 | out | bars (128) + vec (1024)
+    static constexpr int SMEM = USED + 768;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(256) attn_bwd_delta_tc_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout,
+                                                               float* __restrict__ delta, int B, int T, int H) {
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (gw >= B * T * H) return;
+    const int h = gw % H, m = gw / H;
+    const size_t off = (size_t)m * (H * HD) + h * HD + lane * (HD / 32);
+    float s;
+    if (HD == 64) {
+        float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(out + off));
+        float2 d = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(dout + off));
+        s = a.x * d.x + a.y * d.y;
+    } else {
+        uint2 ua = *reinterpret_cast<const uint2*>(out + off), ud = *reinterpret_cast<const uint2*>(dout + off);
+        float2 a0 = unpack_bf16x2(ua.x), a1 = unpack_bf16x2(ua.y), d0 = unpack_bf16x2(ud.x), d1 = unpack_bf16x2(ud.y);
+        s = a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y;
+    }
+    s = warp_sum(s);
+    if (lane == 0) delta[((size_t)(m / T) * H + h) * T + (m % T)] = s;
+}
+
+// tm128 / tm64: qkv viewed [B][T][3d] with 128- / 64-row boxes; tdo128 / tdo64: dO viewed [B][T][d].
+template <int HD, bool DKV>
+__global__ void __launch_bounds__(NTHREADS, HD == 64 ? 2 : 1)
+attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm64,
+                   const __grid_constant__ CUtensorMap tdo128, const __grid_constant__ CUtensorMap tdo64,
+                   const float* __restrict__ lse, const float* __restrict__ delta, bf16* __restrict__ dqkv, int T, int H,
+                   float scale, float scale_log2) {
+    using C = BCfg<HD, DKV>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t sA0 = base;                          // stationary operand of score MMA 1 (K | Q)
+    const uint32_t sA1 = sA0 + C::STAT;                 // stationary operand of score MMA 2 (V | dO)
+    const uint32_t sB0 = sA1 + C::STAT;                 // streamed, 2 stages: (Q_i | K_j)
+    const uint32_t sB1 = sB0 + 2 * C::STR;              // streamed, 2 stages: (dO_i | V_j)
+    const uint32_t sOut = sB1 + 2 * C::STR;             // NOUT tiles [128 x 64] bf16
+    const uint32_t bars = sOut + C::NOUT * SUB;
+    const uint32_t stat_full = bars;
+    auto str_full = [&](int s) { return bars + 8u * (1 + s); };
+    auto str_empty = [&](int s) { return bars + 8u * (3 + s); };
+    const uint32_t sc_full = bars + 8u * 5, sc_empty = bars + 8u * 6;
+    const uint32_t out_full = bars + 8u * 7, out_empty = bars + 8u * 8;
+    const uint32_t acc_done = bars + 8u * 9;
+    const uint32_t tmem_slot = bars + 8u * 10;
+    uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
+    float* s_vec = reinterpret_cast<float*>(gen + (bars + 128 - base));   // [2 stages][lse2(64) | delta(64)]
+    if (base - ptx::smem_u32(smem_raw) > 768u) __trap();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int d_model = H * HD;
+    const int n64 = (T + 63) / 64;
+    // stationary tile index and the range of streamed 64-row tiles
+    const int ts = DKV ? (int)blockIdx.x : (int)(gridDim.x - 1 - blockIdx.x);   // heavy tiles first in both passes
+    const int r0 = ts * 128;                            // first key (DKV) / query (DQ) row of the stationary tile
+    const int it0 = DKV ? 2 * ts : 0;                   // first streamed tile
+    const int it1 = DKV ? n64 : min(n64, 2 * ts + 2);   // one past the last streamed tile
+    const int niter = it1 - it0;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tm128); ptx::prefetch_tmap(&tm64);
+        ptx::prefetch_tmap(&tdo128); ptx::prefetch_tmap(&tdo64);
+    }
+    if (warp == 1 && lane == 0) {
+        ptx::mbar_init(stat_full, 1);
+        for (int s = 0; s < 2; ++s) { ptx::mbar_init(str_full(s), 1); ptx::mbar_init(str_empty(s), 1); }
+        ptx::mbar_init(sc_full, 1);   ptx::mbar_init(sc_empty, 4);
+        ptx::mbar_init(out_full, 4);  ptx::mbar_init(out_empty, 1);
+        ptx::mbar_init(acc_done, 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) {
+        ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base));
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0 && niter > 0) {
+            ptx::mbar_arrive_expect_tx(stat_full, 2 * C::STAT);
+#pragma unroll
+            for (int c = 0; c < C::NSUB; ++c) {
+                if (DKV) {
+                    ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, d_model + h * HD + c * 64, r0, b);        // K
+                    ptx::tma_load_3d(sA1 + c * SUB, &tm128, stat_full, 2 * d_model + h * HD + c * 64, r0, b);    // V
+                } else {
+                    ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, h * HD + c * 64, r0, b);                  // Q
+                    ptx::tma_load_3d(sA1 + c * SUB, &tdo128, stat_full, h * HD + c * 64, r0, b);                 // dO
+                }
+            }
+            for (int n = 0; n < niter; ++n) {
+                const int st = n & 1;
+                const int row0 = (it0 + n) * 64;
+                ptx::mbar_wait(str_empty(st), ((n >> 1) & 1) ^ 1);
+                ptx::mbar_arrive_expect_tx(str_full(st), 2 * C::STR);
+#pragma unroll
+                for (int c = 0; c < C::NSUB; ++c) {
+                    if (DKV) {
+                        ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), h * HD + c * 64, row0, b);    // Q_i
+                        ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tdo64, str_full(st), h * HD + c * 64, row0, b);   // dO_i
+                    } else {
+                        ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), d_model + h * HD + c * 64, row0, b);      // K_j
+                        ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tm64, str_full(st), 2 * d_model + h * HD + c * 64, row0, b);  // V_j
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0 && niter > 0) {
+            constexpr uint32_t id_sc = ptx::umma_idesc_bf16(128, 64, 0, 0);     // scores: both operands K-major
+            constexpr uint32_t id_acc = ptx::umma_idesc_bf16(128, HD, 0, 1);    // accumulate: A K-major (smem out tile), B MN-major
+            ptx::mbar_wait(stat_full, 0);
+            for (int n = 0; n < niter; ++n) {
+                const int st = n & 1;
+                const uint32_t b0 = sB0 + st * C::STR, b1 = sB1 + st * C::STR;
+                ptx::mbar_wait(str_full(st), (n >> 1) & 1);
+                ptx::mbar_wait(sc_empty, (n & 1) ^ 1);
+                ptx::tc_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < HD / 16; ++kk) {
+                    const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
+                    ptx::mma_bf16_ss(tmem + C::SC1, ptx::umma_desc(sA0 + oa, 16, 1024), ptx::umma_desc(b0 + ob, 16, 1024),
+                                     id_sc, kk > 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int kk = 0; kk < HD / 16; ++kk) {
+                    const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
+                    ptx::mma_bf16_ss(tmem + C::SC2, ptx::umma_desc(sA1 + oa, 16, 1024), ptx::umma_desc(b1 + ob, 16, 1024),
+                                     id_sc, kk > 0 ? 1u : 0u);
+                }
+                ptx::mma_commit(sc_full);
+                ptx::mbar_wait(out_full, n & 1);
+                ptx::tc_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {                 // contraction over the 64 streamed rows
+                    const uint32_t acc = (n > 0 || kk > 0) ? 1u : 0u;
+                    if (DKV) {
+                        // dV += P^T dO_i ; dK += dS^T Q_i
+                        ptx::mma_bf16_ss(tmem + C::ACC, ptx::umma_desc(sOut + kk * 32, 16, 1024),
+                                         ptx::umma_desc(b1 + kk * 2048, SUB64, 1024), id_acc, acc);
+                        ptx::mma_bf16_ss(tmem + C::ACC + HD, ptx::umma_desc(sOut + SUB + kk * 32, 16, 1024),
+                                         ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
+                    } else {
+                        // dQ += dS K_j
+                        ptx::mma_bf16_ss(tmem + C::ACC, ptx::umma_desc(sOut + kk * 32, 16, 1024),
+                                         ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
+                    }
+                }
+                ptx::mma_commit(out_empty);
+                ptx::mma_commit(str_empty(st));
+            }
+            ptx::mma_commit(acc_done);
+        }
+    } else {
+        // ------------------------------------------------------------------ elementwise warps (2..5): thread = stationary row
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int srow = r0 + row;                                  // key row (DKV) / query row (DQ)
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        const float* lse_g = lse + ((size_t)b * H + h) * T;
+        const float* del_g = delta + ((size_t)b * H + h) * T;
+        float my_l2 = INFINITY, my_dl = 0.f;
+        if (!DKV && srow < T) { my_l2 = lse_g[srow] * 1.4426950408889634f; my_dl = del_g[srow]; }
+        const int t128 = threadIdx.x - 64;                          // 0..127 among the elementwise threads
+        for (int n = 0; n < niter; ++n) {
+            const int c0 = (it0 + n) * 64;                          // first streamed row = first score column
+            if (DKV) {
+                // per-column (query) statistics of this tile -> smem, double-buffered by parity
+                float* v = s_vec + (n & 1) * 128;
+                const int qq = c0 + (t128 & 63);
+                if (t128 < 64) v[t128] = qq < T ? lse_g[qq] * 1.4426950408889634f : INFINITY;
+                else v[t128] = qq < T ? del_g[qq] : 0.f;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
+            const float* vl = s_vec + (n & 1) * 128;
+            // causal mask is needed only where the streamed tile overlaps the diagonal
+            const bool need_mask = DKV ? (c0 < r0 + 128) : (c0 + 63 > r0);
+            ptx::mbar_wait(sc_full, n & 1);
+            ptx::tc_fence_after();
+            ptx::mbar_wait(out_empty, (n & 1) ^ 1);
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t rs[32], rp[32];
+                ptx::tmem_ld_32x32(tmem + lane_off + C::SC1 + c * 32, rs);
+                ptx::tmem_ld_32x32(tmem + lane_off + C::SC2 + c * 32, rp);
+                ptx::tmem_ld_wait();
+                if (c == 1) {
+                    // both score tiles are in registers: the MMA warp may overwrite them
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(sc_empty);
+                }
+                uint32_t pk[16], dk[16];
+#pragma unroll
+                for (int e = 0; e < 32; e += 2) {
+                    const int col = c * 32 + e;
+                    const float l2a = DKV ? vl[col] : my_l2, l2b = DKV ? vl[col + 1] : my_l2;
+                    const float dla = DKV ? vl[64 + col] : my_dl, dlb = DKV ? vl[64 + col + 1] : my_dl;
+                    float p0 = exp2f(__uint_as_float(rs[e]) * scale_log2 - l2a);
+                    float p1 = exp2f(__uint_as_float(rs[e + 1]) * scale_log2 - l2b);
+                    if (need_mask) {
+                        // key index must be <= query index
+                        const int key0 = DKV ? srow : c0 + col, qry0 = DKV ? c0 + col : srow;
+                        const int key1 = DKV ? srow : key0 + 1, qry1 = DKV ? qry0 + 1 : srow;
+                        if (key0 > qry0) p0 = 0.f;
+                        if (key1 > qry1) p1 = 0.f;
+                    }
+                    if (DKV ? (srow >= T) : (c0 + col >= T)) p0 = 0.f;          // zero-filled key rows
+                    if (DKV ? (srow >= T) : (c0 + col + 1 >= T)) p1 = 0.f;
+                    const float s0 = p0 * (__uint_as_float(rp[e]) - dla) * scale;
+                    const float s1 = p1 * (__uint_as_float(rp[e + 1]) - dlb) * scale;
+                    pk[e >> 1] = pack_bf16x2(p0, p1);
+                    dk[e >> 1] = pack_bf16x2(s0, s1);
+                }
+                const uint32_t dst = sOut + row * 128;
+#pragma unroll
+                for (int ch = 0; ch < 4; ++ch) {
+                    const uint32_t sw = (((uint32_t)(c * 4 + ch)) ^ ((uint32_t)row & 7u)) << 4;
+                    if (DKV) {
+                        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]),
+                                     "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3]) : "memory");
+                        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + SUB + sw), "r"(dk[4 * ch]),
+                                     "r"(dk[4 * ch + 1]), "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
+                    } else {
+                        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(dk[4 * ch]), "r"(dk[4 * ch + 1]),
+                                     "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
+                    }
+                }
+            }
+            ptx::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(out_full);
+        }
+        // ---- epilogue: accumulator rows -> bf16 -> dqkv (thread = stationary row)
+        if (niter > 0) {
+            ptx::mbar_wait(acc_done, 0);
+            ptx::tc_fence_after();
+        }
+        bf16* g0 = dqkv + ((size_t)b * T + srow) * (3 * d_model) + h * HD + (DKV ? 2 * d_model : 0);   // dV | dQ
+        bf16* g1 = dqkv + ((size_t)b * T + srow) * (3 * d_model) + h * HD + d_model;                    // dK
+#pragma unroll 1
+        for (int c = 0; c < HD / 32; ++c) {
+            uint32_t r0v[32], r1v[32];
+            if (niter > 0) {
+                ptx::tmem_ld_32x32(tmem + lane_off + C::ACC + c * 32, r0v);
+                if (DKV) ptx::tmem_ld_32x32(tmem + lane_off + C::ACC + HD + c * 32, r1v);
+                ptx::tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int e = 0; e < 32; ++e) { r0v[e] = 0u; r1v[e] = 0u; }
+            }
+            if (srow < T) {
+#pragma unroll
+                for (int e = 0; e < 32; e += 8) {
+                    *reinterpret_cast<uint4*>(g0 + c * 32 + e) =
+                        make_uint4(pack_bf16x2(__uint_as_float(r0v[e]), __uint_as_float(r0v[e + 1])),
+                                   pack_bf16x2(__uint_as_float(r0v[e + 2]), __uint_as_float(r0v[e + 3])),
+                                   pack_bf16x2(__uint_as_float(r0v[e + 4]), __uint_as_float(r0v[e + 5])),
+                                   pack_bf16x2(__uint_as_float(r0v[e + 6]), __uint_as_float(r0v[e + 7])));
+                    if (DKV)
+                        *reinterpret_cast<uint4*>(g1 + c * 32 + e) =
+                            make_uint4(pack_bf16x2(__uint_as_float(r1v[e]), __uint_as_float(r1v[e + 1])),
+                                       pack_bf16x2(__uint_as_float(r1v[e + 2]), __uint_as_float(r1v[e + 3])),
+                                       pack_bf16x2(__uint_as_float(r1v[e + 4]), __uint_as_float(r1v[e + 5])),
+                                       pack_bf16x2(__uint_as_float(r1v[e + 6]), __uint_as_float(r1v[e + 7])));
+                }
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem, C::TMEM_COLS);
+    }
+}
+
+template <int HD, bool DKV>
+int launch_bwd_pass(const CUtensorMap& t128, const CUtensorMap& t64, const CUtensorMap& d128, const CUtensorMap& d64,
+                    const float* lse, const float* delta, void* dqkv, int B, int T, int H, float scale, cudaStream_t st) {
+    using C = BCfg<HD, DKV>;
+    auto kern = attn_bwd_tc_kernel<HD, DKV>;
+    static bool cfg = false;
+    if (!cfg) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+        cfg = true;
+    }
+    dim3 grid((T + 127) / 128, H, B);
+    kern<<<grid, NTHREADS, C::SMEM, st>>>(t128, t64, d128, d64, lse, delta, (bf16*)dqkv, T, H, scale,
+                                          scale * 1.4426950408889634f);
+    return 0;
+}
+
+template <int HD>
+int launch_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, void* dqkv, int B, int T,
+               int H, float scale, cudaStream_t st) {
+    const int d = H * HD;
+    CUtensorMap t128, t64, d128, d64;
+    if (tma::make_3d(&t128, qkv, 3 * d, T, B, (uint64_t)3 * d * 2, (uint64_t)T * 3 * d * 2, 64, 128, 2)) return -1;
+    if (tma::make_3d(&t64, qkv, 3 * d, T, B, (uint64_t)3 * d * 2, (uint64_t)T * 3 * d * 2, 64, 64, 2)) return -1;
+    if (tma::make_3d(&d128, dout, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 128, 2)) return -1;
+    if (tma::make_3d(&d64, dout, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 64, 2)) return -1;
+    const int total_warps = B * T * H;
+    attn_bwd_delta_tc_kernel<HD><<<(total_warps + 7) / 8, 256, 0, st>>>((const bf16*)out, (const bf16*)dout, delta, B, T, H);
+    if (launch_bwd_pass<HD, true>(t128, t64, d128, d64, lse, delta, dqkv, B, T, H, scale, st)) return -1;
+    if (launch_bwd_pass<HD, false>(t128, t64, d128, d64, lse, delta, dqkv, B, T, H, scale, st)) return -1;
+    return 0;
+}
+
 }  // namespace
 
 extern "C" int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale,
@@ -311,4 +661,14 @@ extern "C" int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, i
     int rc = hs == 64 ? launch_fwd<64>(qkv, out, lse, B, T, H, scale, st) : launch_fwd<128>(qkv, out, lse, B, T, H, scale, st);
     if (rc) return rc;
     B200_RETURN_LAUNCH_STATUS("attn_fwd_tc");
+}
+
+// delta: [B, H, T] fp32 scratch (row sums of dO * O); nothing else is needed.
+extern "C" int b200_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                                void* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t st) {
+    B200_REQUIRE(hs == 64 || hs == 128, "attn_bwd_tc: head size must be 64 or 128 (got %d)", hs);
+    int rc = hs == 64 ? launch_bwd<64>(qkv, out, dout, lse, delta, dqkv, B, T, H, scale, st)
+                      : launch_bwd<128>(qkv, out, dout, lse, delta, dqkv, B, T, H, scale, st);
+    if (rc) return rc;
+    B200_RETURN_LAUNCH_STATUS("attn_bwd_tc");
 }

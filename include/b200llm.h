@@ -83,6 +83,10 @@ int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H
 /* dqkv [B*T, 3*H*hs] bf16; delta [B, H, T] fp32 scratch; dq_acc [B*T, H*hs] fp32 scratch */
 int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t st);
 
+/* tcgen05 backward, two passes of one kernel (key-stationary: dK, dV; query-stationary: dQ), all
+ * accumulators in TMEM, no atomics; delta [B, H, T] fp32 is the only scratch. */
+int b200_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, void* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t st);
+
 /* ---- generation (ref: src/models/transformer.py:96-114) ------------------------------------
  * pos_dev (nullable, device int): when given it overrides pos0 / len (= *pos_dev + 1) / adds to the
  * sampler step, so that one captured CUDA graph can be replayed for every decode position.

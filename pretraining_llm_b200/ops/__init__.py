@@ -29,7 +29,7 @@ def _p(t: Optional[torch.Tensor]) -> Optional[int]:
 
 LAUNCHES = 0   # kernels of this library enqueued so far (bench.py reports the count per timed region)
 
-_KERNELS_PER_CALL = {"embed_bwd": 2, "ln_bwd": 2, "attn_bwd": 3}
+_KERNELS_PER_CALL = {"embed_bwd": 2, "ln_bwd": 2, "attn_bwd": 3, "attn_bwd_tc": 3}
 
 
 def _chk(rc: int, what: str) -> None:
@@ -185,15 +185,25 @@ def attn_fwd(qkv, B, T, H, hs, out=None, lse=None, impl: Optional[str] = None):
     return out, lse
 
 
-def attn_bwd(qkv, out, dout, lse, B, T, H, hs, dqkv=None, delta=None, dq_acc=None):
+ATTN_BWD_IMPL = os.environ.get("B200_ATTN_BWD", "tc")
+
+
+def attn_bwd(qkv, out, dout, lse, B, T, H, hs, dqkv=None, delta=None, dq_acc=None, counters=None,
+             impl: Optional[str] = None):
+    """Default: the tcgen05 two-pass backward (only `delta` scratch).  impl="mma": the mma.sync kernel, which
+    also needs dq_acc (fp32 [B*T, H*hs], zero on entry, left zero)."""
     if dqkv is None:
         dqkv = torch.empty_like(qkv)
     if delta is None:
         delta = torch.empty(B, H, T, device=qkv.device, dtype=F32)
-    if dq_acc is None:
-        dq_acc = torch.zeros(B * T, H * hs, device=qkv.device, dtype=F32)
-    _chk(lib.load().b200_attn_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_acc), _p(dqkv), B, T, H, hs,
-                                  1.0 / math.sqrt(hs), _st()), "attn_bwd")
+    if (impl or ATTN_BWD_IMPL) == "tc":
+        _chk(lib.load().b200_attn_bwd_tc(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dqkv), B, T, H, hs,
+                                         1.0 / math.sqrt(hs), _st()), "attn_bwd_tc")
+    else:
+        if dq_acc is None:
+            dq_acc = torch.zeros(B * T, H * hs, device=qkv.device, dtype=F32)
+        _chk(lib.load().b200_attn_bwd(_p(qkv), _p(out), _p(dout), _p(lse), _p(delta), _p(dq_acc), _p(dqkv), B, T, H,
+                                      hs, 1.0 / math.sqrt(hs), _st()), "attn_bwd")
     return dqkv
 
 

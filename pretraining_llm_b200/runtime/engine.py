@@ -72,7 +72,7 @@ class Workspace:
             self.dqkv = e(M, 3 * d)
             self.dtmp = e(M, d)
             self.delta = e(B, H, T, dt=F32)
-            self.dq_acc = torch.zeros(M, d, device=dev, dtype=F32)
+            self.dq_acc = torch.zeros(M, d, device=dev, dtype=F32) if ops.ATTN_BWD_IMPL != "tc" else None
             self.ln_partial = e(max(ops.ln_bwd_nparts(M, d), 1) * 3 * d, dt=F32)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
 

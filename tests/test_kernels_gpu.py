@@ -216,7 +216,7 @@ def test_flash_attention_fwd_bwd(ops, hs, T, impl):
     assert torch.allclose(lse, torch.logsumexp(s, -1), atol=2e-3, rtol=1e-3)
     dout = _rand(B * T, H * hs)
     ref.backward(dout.float())
-    dqkv = ops.attn_bwd(qkv, out, dout, lse, B, T, H, hs)
+    dqkv = ops.attn_bwd(qkv, out, dout, lse, B, T, H, hs, impl=impl)
     g = qr.grad.view(B * T, 3, H * hs)
     mine = dqkv.float().view(B * T, 3, H * hs)
     floor = 1e-3 * dout.float().norm()   # T == 1: dq is exactly 0 in exact arithmetic

@@ -19,3 +19,7 @@ for hs, H, B, T in ((64, 12, 16, 1024), (128, 16, 8, 2048), (64, 12, 4, 4096)):
         out, lse = ops.attn_fwd(qkv, B, T, H, hs, impl=impl)
         ms = timeit(lambda: ops.attn_fwd(qkv, B, T, H, hs, out=out, lse=lse, impl=impl))
         print(f"attn fwd {impl} hs{hs} B{B} T{T} H{H}: {ms:.4f} ms  {fl/ms/1e9:.1f} TFLOP/s", flush=True)
+        dout = torch.randn_like(out); dqkv = torch.empty_like(qkv); delta = torch.empty(B, H, T, device="cuda")
+        dq = torch.zeros(B*T, H*hs, device="cuda"); 
+        ms = timeit(lambda: ops.attn_bwd(qkv, out, dout, lse, B, T, H, hs, dqkv=dqkv, delta=delta, dq_acc=dq, impl=impl))
+        print(f"attn bwd {impl} hs{hs} B{B} T{T} H{H}: {ms:.4f} ms  {2.5*fl/ms/1e9:.1f} TFLOP/s", flush=True)
