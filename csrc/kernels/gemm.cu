@@ -36,7 +36,7 @@ template <int BN> struct Cfg {
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
     static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * EPI_BUF_BYTES + 256 /*barriers*/ + 1024 /*align*/;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * EPI_BUF_BYTES + 256 /*barriers*/ + 1024 /*bias tile*/ + 1024 /*align*/;
 };
 
 struct Params {
@@ -71,6 +71,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + 2 + s); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 4);
     uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));  // generic pointer to aligned base
+    float* s_bias = reinterpret_cast<float*>(smem_gen + (bar_base + 256 - smem_base));   // [256] bias of the current tile
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -187,12 +188,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const int n_blk = tile / p.num_m;
             const int m0 = (tile % p.num_m) * BM, n0 = n_blk * BN;
             const int m = m0 + row;
+            if (!OUT_F32 && p.bias != nullptr) {
+                // stage this tile's bias slice in smem while the MMAs are still running
+                asm volatile("bar.sync 1, 128;" ::: "memory");          // previous tile's readers are done
+                const int et = threadIdx.x - 64;
+                for (int j = et; j < BN; j += 128) s_bias[j] = (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
             ptx::mbar_wait(tfull_bar(acc), acc_phase);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
             float run_max = -INFINITY, run_sum = 0.f;
 #pragma unroll 1
             for (int c = 0; c < BN / 64; ++c) {
+                const int nc0 = n0 + c * 64;
+                uint4 mk4[8];
+                if (!OUT_F32 && p.mask != nullptr && m < p.M) {
+                    const bf16* mk = p.mask + (size_t)m * p.ld_mask + nc0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        mk4[j] = (nc0 + j * 8 < p.N) ? ldg_stream_u4(reinterpret_cast<const uint4*>(mk + j * 8))
+                                                     : make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+                }
                 uint32_t r[64];
                 {
                     uint32_t(&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[0]);
@@ -207,7 +224,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     __syncwarp();
                     if (lane == 0) ptx::mbar_arrive(tempty_bar(acc));
                 }
-                const int nc0 = n0 + c * 64;
                 if (OUT_F32) {
                     if (m < p.M) {
                         float* o = p.out_f32 + (size_t)m * p.ldc + nc0;
@@ -240,13 +256,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     if (p.bias != nullptr) {
 #pragma unroll
                         for (int j = 0; j < 64; j += 4) {
-                            if (nc0 + j < p.N) {
-                                float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + nc0 + j));
-                                r[j] = __float_as_uint(__uint_as_float(r[j]) + b.x);
-                                r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b.y);
-                                r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + b.z);
-                                r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b.w);
-                            }
+                            const float4 b = *reinterpret_cast<const float4*>(s_bias + c * 64 + j);   // smem broadcast
+                            r[j] = __float_as_uint(__uint_as_float(r[j]) + b.x);
+                            r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b.y);
+                            r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + b.z);
+                            r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b.w);
                         }
                     }
                     if (p.relu) {
@@ -254,18 +268,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                         for (int j = 0; j < 64; ++j) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
                     }
                     if (p.mask != nullptr && m < p.M) {
-                        const bf16* mk = p.mask + (size_t)m * p.ld_mask + nc0;
 #pragma unroll
-                        for (int j = 0; j < 64; j += 8) {
-                            if (nc0 + j < p.N) {  // N % 8 == 0 required with a mask
-                                uint4 u4 = *reinterpret_cast<const uint4*>(mk + j);
-                                const uint32_t w[4] = {u4.x, u4.y, u4.z, u4.w};
+                        for (int j = 0; j < 8; ++j) {
+                            const uint32_t w[4] = {mk4[j].x, mk4[j].y, mk4[j].z, mk4[j].w};
 #pragma unroll
-                                for (int t = 0; t < 4; ++t) {
-                                    float2 f = unpack_bf16x2(w[t]);
-                                    if (!(f.x > 0.f)) r[j + 2 * t] = 0u;
-                                    if (!(f.y > 0.f)) r[j + 2 * t + 1] = 0u;
-                                }
+                            for (int t = 0; t < 4; ++t) {
+                                float2 f = unpack_bf16x2(w[t]);
+                                if (!(f.x > 0.f)) r[j * 8 + 2 * t] = 0u;
+                                if (!(f.y > 0.f)) r[j * 8 + 2 * t + 1] = 0u;
                             }
                         }
                     }

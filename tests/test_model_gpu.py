@@ -143,10 +143,14 @@ def test_generate_cache_matches_recompute_and_torch():
     idx = torch.randint(0, V, (3, 9), device="cuda")
     g = torch.Generator().manual_seed(5)
     out_c, log_c = native.engine.generate(idx, 12, generator=g, return_logits=True)
-    g = torch.Generator().manual_seed(5)
-    out_r, log_r = native.engine.generate(idx, 12, generator=g, return_logits=True, use_cache=False)
-    for a, b in zip(log_c, log_r):
-        assert _rel(a, b) < 3e-2
+    # the same trajectory re-scored without the cache (one full forward): step-wise logits must agree.
+    # (Two independently sampled runs are not comparable: a bf16-level logit difference can flip a draw.)
+    with torch.no_grad():
+        _, full_native, _ = native.engine.forward(out_c[:, :-1].contiguous())
+    for k, a in enumerate(log_c):
+        assert _rel(a, full_native[:, 9 + k - 1].float()) < 3e-2, k
+    out_r = native.engine.generate(idx, 12, generator=torch.Generator().manual_seed(5), use_cache=False)
+    assert out_r.shape == out_c.shape and torch.equal(out_r[:, :9], idx)
     # logits along the native trajectory agree with the PyTorch model evaluated on the same prefix
     with torch.autocast("cuda", dtype=torch.bfloat16):
         full, _ = oracle(out_c[:, :-1])
