@@ -22,13 +22,15 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tma.cuh"
+#include "gemm_epilogue.cuh"
 
 namespace {
 
+using gemm::Params;
+using gemm::EPI_BUF_BYTES;
 constexpr int BM = 128;
 constexpr int BK = 64;               // 64 bf16 = 128 bytes = one swizzle row
 constexpr int A_BYTES = BM * BK * 2; // 16 KiB
-constexpr int EPI_BUF_BYTES = BM * 64 * 2;  // one 128 x 64 bf16 staging tile
 constexpr int NUM_THREADS = 192;
 
 template <int BN> struct Cfg {
@@ -39,21 +41,6 @@ template <int BN> struct Cfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * EPI_BUF_BYTES + 256 /*barriers*/ + 1024 /*bias tile*/ + 1024 /*align*/;
 };
 
-struct Params {
-    int M, N, K;
-    int num_m, num_n, num_kb, splits, kb_per_split;
-    float alpha;
-    // bf16 epilogue
-    const float* bias;      // [N] or null
-    int relu;               // apply max(0, .)
-    const bf16* mask;       // [M, ld_mask] post-ReLU activations: out = mask > 0 ? v : 0
-    int ld_mask;
-    float2* stats;          // [num_n][M] (max, sum exp) of the bf16-rounded outputs, or null
-    // fp32 epilogue
-    float* out_f32;
-    long long ldc;
-    int f32_mode;           // 0 store, 1 accumulate (+=), 2 atomic add
-};
 
 template <int BN, bool A_MN, bool B_MN, bool OUT_F32>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -187,147 +174,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const int tile = u % ntiles;
             const int n_blk = tile / p.num_m;
             const int m0 = (tile % p.num_m) * BM, n0 = n_blk * BN;
-            const int m = m0 + row;
-            if (!OUT_F32 && p.bias != nullptr) {
-                // stage this tile's bias slice in smem while the MMAs are still running
-                asm volatile("bar.sync 1, 128;" ::: "memory");          // previous tile's readers are done
-                const int et = threadIdx.x - 64;
-                for (int j = et; j < BN; j += 128) s_bias[j] = (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-            }
-            ptx::mbar_wait(tfull_bar(acc), acc_phase);
-            ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
-            float run_max = -INFINITY, run_sum = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < BN / 64; ++c) {
-                const int nc0 = n0 + c * 64;
-                uint4 mk4[8];
-                if (!OUT_F32 && p.mask != nullptr && m < p.M) {
-                    const bf16* mk = p.mask + (size_t)m * p.ld_mask + nc0;
-#pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        mk4[j] = (nc0 + j * 8 < p.N) ? ldg_stream_u4(reinterpret_cast<const uint4*>(mk + j * 8))
-                                                     : make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-                }
-                uint32_t r[64];
-                {
-                    uint32_t(&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[0]);
-                    uint32_t(&r1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[32]);
-                    ptx::tmem_ld_32x32(taddr + c * 64, r0);
-                    ptx::tmem_ld_32x32(taddr + c * 64 + 32, r1);
-                    ptx::tmem_ld_wait();
-                }
-                if (c == BN / 64 - 1) {
-                    // all TMEM reads of this accumulator stage are done: hand it back to the MMA warp
-                    ptx::tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(tempty_bar(acc));
-                }
-                if (OUT_F32) {
-                    if (m < p.M) {
-                        float* o = p.out_f32 + (size_t)m * p.ldc + nc0;
-#pragma unroll
-                        for (int j = 0; j < 64; j += 4) {
-                            if (nc0 + j < p.N) {  // N % 4 == 0 is required by the host wrapper
-                                float4 v = make_float4(__uint_as_float(r[j]) * p.alpha, __uint_as_float(r[j + 1]) * p.alpha,
-                                                       __uint_as_float(r[j + 2]) * p.alpha,
-                                                       __uint_as_float(r[j + 3]) * p.alpha);
-                                if (p.f32_mode == 2) {
-                                    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(o + j), "f"(v.x),
-                                                 "f"(v.y), "f"(v.z), "f"(v.w)
-                                                 : "memory");
-                                } else {
-                                    if (p.f32_mode == 1) {
-                                        float4 old = *reinterpret_cast<float4*>(o + j);
-                                        v.x += old.x; v.y += old.y; v.z += old.z; v.w += old.w;
-                                    }
-                                    *reinterpret_cast<float4*>(o + j) = v;
-                                }
-                            }
-                        }
-                    }
-                } else {
-                    // ---- elementwise epilogue in fp32 registers
-                    if (p.alpha != 1.f) {
-#pragma unroll
-                        for (int j = 0; j < 64; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
-                    }
-                    if (p.bias != nullptr) {
-#pragma unroll
-                        for (int j = 0; j < 64; j += 4) {
-                            const float4 b = *reinterpret_cast<const float4*>(s_bias + c * 64 + j);   // smem broadcast
-                            r[j] = __float_as_uint(__uint_as_float(r[j]) + b.x);
-                            r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b.y);
-                            r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + b.z);
-                            r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b.w);
-                        }
-                    }
-                    if (p.relu) {
-#pragma unroll
-                        for (int j = 0; j < 64; ++j) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
-                    }
-                    if (p.mask != nullptr && m < p.M) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const uint32_t w[4] = {mk4[j].x, mk4[j].y, mk4[j].z, mk4[j].w};
-#pragma unroll
-                            for (int t = 0; t < 4; ++t) {
-                                float2 f = unpack_bf16x2(w[t]);
-                                if (!(f.x > 0.f)) r[j * 8 + 2 * t] = 0u;
-                                if (!(f.y > 0.f)) r[j * 8 + 2 * t + 1] = 0u;
-                            }
-                        }
-                    }
-                    // ---- pack to bf16
-                    uint32_t pk[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        pk[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
-                    if (p.stats != nullptr) {
-                        // online softmax statistics over the bf16-rounded values (what CE will see)
-                        float cmax = -INFINITY;
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            float2 f = unpack_bf16x2(pk[j]);
-                            if (nc0 + 2 * j < p.N) cmax = fmaxf(cmax, f.x);
-                            if (nc0 + 2 * j + 1 < p.N) cmax = fmaxf(cmax, f.y);
-                        }
-                        const float new_max = fmaxf(run_max, cmax);
-                        if (new_max > -INFINITY) {
-                            float s = 0.f;
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                float2 f = unpack_bf16x2(pk[j]);
-                                if (nc0 + 2 * j < p.N) s += __expf(f.x - new_max);
-                                if (nc0 + 2 * j + 1 < p.N) s += __expf(f.y - new_max);
-                            }
-                            run_sum = run_sum * __expf(run_max - new_max) + s;
-                            run_max = new_max;
-                        }
-                    }
-                    // ---- stage in swizzled smem, then one thread issues the TMA store
-                    if (store_thread) ptx::tma_store_wait_read<1>();  // buffer `buf` (2 stores ago) is drained
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    const uint32_t sdst = epi_base + buf * EPI_BUF_BYTES + row * 128;
-#pragma unroll
-                    for (int ch = 0; ch < 8; ++ch) {
-                        const uint32_t addr = sdst + (((uint32_t)ch ^ ((uint32_t)row & 7u)) << 4);
-                        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(pk[4 * ch]),
-                                     "r"(pk[4 * ch + 1]), "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3])
-                                     : "memory");
-                    }
-                    ptx::fence_proxy_async_smem();
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    if (store_thread) {
-                        if (nc0 < p.N) ptx::tma_store_2d(&tmC, epi_base + buf * EPI_BUF_BYTES, nc0, m0);
-                        ptx::tma_store_commit();
-                    }
-                    buf ^= 1;
-                }
-            }
-            if (!OUT_F32 && p.stats != nullptr && m < p.M)
-                p.stats[(size_t)n_blk * p.M + m] = make_float2(run_max, run_sum);
+            const uint32_t te = tempty_bar(acc);
+            gemm::epilogue_tile<BN, OUT_F32>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base, buf,
+                                             store_thread, s_bias, (int)threadIdx.x - 64, [te]() { ptx::mbar_arrive(te); });
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (!OUT_F32 && store_thread) ptx::tma_store_wait_all<0>();

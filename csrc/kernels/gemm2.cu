@@ -1,0 +1,259 @@
+// 2-CTA (cta_group::2) variant of the tcgen05 GEMM: a CTA PAIR (two SMs of one TPC, a cluster of 2)
+// computes a 256 x BN tile.  Each CTA stages only ITS half of the operands - its 128 rows of A and
+// its BN/2 rows of B - and the leader CTA issues tcgen05.mma.cta_group::2 (M = 256), which reads both
+// halves out of both CTAs' shared memory.  Per MMA that is 1.5x fewer shared-memory bytes per CTA
+// than the 1-CTA kernel (32 KiB instead of 48 KiB per 64-deep k-block at BN = 256), so the same
+// 192 KiB of smem holds 6 pipeline stages instead of 4: the k-loop survives the L2 -> smem latency
+// that the ncu profile of the 1-CTA kernel showed it was bound by (tensor pipe 52-70 % active).
+//
+//   TMA loads of both CTAs are credited to the LEADER's full barrier; the leader's MMA thread commits
+//   with a multicast arrive to the empty / accumulator-full barriers of BOTH CTAs; each CTA's epilogue
+//   warps drain their own 128 TMEM lanes and arrive (remotely for the follower) on the leader's
+//   accumulator-empty barrier.  Epilogues, operand majors and split-K are those of gemm.cu.
+#include <cuda.h>
+
+#include "b200llm.h"
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tma.cuh"
+#include "gemm_epilogue.cuh"
+
+namespace {
+
+using gemm::Params;
+using gemm::EPI_BUF_BYTES;
+constexpr int BK = 64;
+constexpr int A_BYTES = 128 * BK * 2;   // this CTA's 128 rows of A
+constexpr int NUM_THREADS = 192;
+
+template <int BN> struct Cfg2 {
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;          // this CTA's half of the B tile
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = BN == 256 ? 6 : 8;
+    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * EPI_BUF_BYTES + 256 + 1024 + 1024;
+};
+
+template <int BN, bool A_MN, bool B_MN, bool OUT_F32>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+             const __grid_constant__ CUtensorMap tmC, const Params p) {
+    using C = Cfg2<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t epi_base = smem_base + C::STAGES * C::STAGE_BYTES;
+    const uint32_t bar_base = epi_base + 2 * EPI_BUF_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + 2 + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 4);
+    uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+    float* s_bias = reinterpret_cast<float*>(smem_gen + (bar_base + 256 - smem_base));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();      // 0 = leader
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmB);
+        if (!OUT_F32) ptx::prefetch_tmap(&tmC);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < C::STAGES; ++s) {
+            ptx::mbar_init(full_bar(s), 1);      // leader's producer arrives (+ transaction bytes of both CTAs)
+            ptx::mbar_init(empty_bar(s), 1);     // multicast commit from the leader's MMA thread
+        }
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(tfull_bar(s), 1);     // multicast commit
+            ptx::mbar_init(tempty_bar(s), 8);    // 4 epilogue warps x 2 CTAs (used in the leader only)
+        }
+        ptx::fence_mbar_init();
+    }
+    ptx::cluster_sync_all();                     // barriers of both CTAs exist before anyone signals them
+    if (warp == 2) {
+        ptx::tmem_alloc_2sm(tmem_slot, C::TMEM_COLS);
+        ptx::tmem_relinquish_2sm();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+    const int ntiles = p.num_m * p.num_n;        // num_m counts 256-row tiles here
+    const int nunits = ntiles * p.splits;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer (both CTAs)
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int u = pair; u < nunits; u += npairs) {
+                const int tile = u % ntiles, split = u / ntiles;
+                const int m0 = (tile % p.num_m) * 256 + (int)rank * 128;
+                const int n0 = (tile / p.num_m) * BN + (int)rank * (BN / 2);
+                const int kb0 = split * p.kb_per_split;
+                const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    ptx::mbar_wait(empty_bar(stage), phase ^ 1);
+                    if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+                    const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+                    const uint32_t sb = sa + A_BYTES;
+                    if (!A_MN) {
+                        ptx::tma_load_2d_2sm(sa, &tmA, full_bar(stage), kb * BK, m0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 2; ++j)
+                            ptx::tma_load_2d_2sm(sa + j * 8192, &tmA, full_bar(stage), m0 + j * 64, kb * BK);
+                    }
+                    if (!B_MN) {
+                        ptx::tma_load_2d_2sm(sb, &tmB, full_bar(stage), kb * BK, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 128; ++j)
+                            ptx::tma_load_2d_2sm(sb + j * 8192, &tmB, full_bar(stage), n0 + j * 64, kb * BK);
+                    }
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc_bf16(256, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            constexpr uint32_t A_LBO = A_MN ? 8192 : 16, B_LBO = B_MN ? 8192 : 16;
+            constexpr uint32_t A_KSTEP = A_MN ? 2048 : 32, B_KSTEP = B_MN ? 2048 : 32;
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int u = pair; u < nunits; u += npairs) {
+                const int split = u / ntiles;
+                const int kb0 = split * p.kb_per_split;
+                const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+                ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    ptx::mbar_wait(full_bar(stage), phase);
+                    ptx::tc_fence_after();
+                    const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+                    const uint32_t sb = sa + A_BYTES;
+                    const uint64_t adesc = ptx::umma_desc(sa, A_LBO, 1024);
+                    const uint64_t bdesc = ptx::umma_desc(sb, B_LBO, 1024);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        ptx::mma_bf16_ss_2sm(tmem_d, adesc + (uint64_t)((k * A_KSTEP) >> 4),
+                                             bdesc + (uint64_t)((k * B_KSTEP) >> 4), idesc,
+                                             (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    ptx::mma_commit_2sm(empty_bar(stage), 3);    // slot free in both CTAs
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+                ptx::mma_commit_2sm(tfull_bar(acc), 3);          // accumulators complete in both CTAs
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const bool store_thread = (threadIdx.x == 64);
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        int buf = 0;
+        for (int u = pair; u < nunits; u += npairs) {
+            const int tile = u % ntiles;
+            const int n_blk = tile / p.num_m;
+            const int m0 = (tile % p.num_m) * 256 + (int)rank * 128, n0 = n_blk * BN;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+            const uint32_t te = ptx::mapa(tempty_bar(acc), 0);   // the leader's accumulator-empty barrier
+            gemm::epilogue_tile<BN, OUT_F32>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base,
+                                             buf, store_thread, s_bias, (int)threadIdx.x - 64,
+                                             [te]() { ptx::mbar_arrive_cluster(te); });
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (!OUT_F32 && store_thread) ptx::tma_store_wait_all<0>();
+    }
+
+    ptx::tc_fence_before();
+    ptx::cluster_sync_all();                     // nobody frees TMEM / exits while the peer may still touch it
+    if (warp == 2) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_2sm(tmem_base, C::TMEM_COLS);
+    }
+}
+
+template <int BN, bool A_MN, bool B_MN, bool OUT_F32>
+int launch2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const Params& p, int grid, cudaStream_t st) {
+    auto kern = gemm2_kernel<BN, A_MN, B_MN, OUT_F32>;
+    static bool configured = false;
+    if (!configured) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::SMEM_BYTES));
+        configured = true;
+    }
+    kern<<<grid, NUM_THREADS, Cfg2<BN>::SMEM_BYTES, st>>>(tA, tB, tC, p);
+    return 0;
+}
+
+template <int BN, bool OUT_F32>
+int launch2_major(int a_mn, int b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const Params& p,
+                  int grid, cudaStream_t st) {
+    if (!a_mn && !b_mn) return launch2<BN, false, false, OUT_F32>(tA, tB, tC, p, grid, st);
+    if (!a_mn && b_mn) return launch2<BN, false, true, OUT_F32>(tA, tB, tC, p, grid, st);
+    if (a_mn && b_mn) return launch2<BN, true, true, OUT_F32>(tA, tB, tC, p, grid, st);
+    return launch2<BN, true, false, OUT_F32>(tA, tB, tC, p, grid, st);
+}
+
+}  // namespace
+
+// Same contract as b200_gemm, tiles of 256 x bn (bn = 256 or 128) on CTA pairs.
+extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, int N, int K, long long lda, long long ldb,
+                              long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias,
+                              int relu, const void* mask, int ld_mask, void* stats, int bn, int split_k, cudaStream_t st) {
+    B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_2cta: empty problem");
+    B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_2cta: lda/ldb must be multiples of 8 elements");
+    B200_REQUIRE(out_f32 ? (ldc % 4 == 0 && N % 4 == 0) : (ldc % 8 == 0), "gemm_2cta: bad ldc / N alignment");
+    B200_REQUIRE(mask == nullptr || (N % 8 == 0 && ld_mask % 8 == 0), "gemm_2cta: mask needs N, ld_mask multiples of 8");
+    const int BN = bn > 0 ? bn : 256;
+    B200_REQUIRE(BN == 256 || BN == 128, "gemm_2cta: bn must be 128 or 256");
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = N; p.K = K;
+    p.num_m = (M + 255) / 256;
+    p.num_n = (N + BN - 1) / BN;
+    p.num_kb = (K + BK - 1) / BK;
+    const int sms = b200_num_sms();
+    int splits = split_k > 0 ? split_k : 1;
+    if (split_k == 0 && out_f32 && f32_mode == 2) {
+        const int tiles = p.num_m * p.num_n;
+        splits = max(1, min(p.num_kb / 4, (3 * (sms / 2)) / max(tiles, 1)));
+    }
+    splits = max(1, min(splits, p.num_kb));
+    p.kb_per_split = (p.num_kb + splits - 1) / splits;
+    splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+    p.splits = splits;
+    B200_REQUIRE(splits == 1 || (out_f32 && f32_mode == 2), "gemm_2cta: split-K needs the atomic fp32 epilogue");
+    p.alpha = alpha;
+    p.bias = bias; p.relu = relu; p.mask = (const bf16*)mask; p.ld_mask = ld_mask; p.stats = (float2*)stats;
+    p.out_f32 = (float*)Cout; p.ldc = ldc; p.f32_mode = f32_mode;
+
+    CUtensorMap tA, tB, tC;
+    memset(&tC, 0, sizeof(tC));
+    if (!a_mn) { if (tma::make_2d(&tA, A, M, K, lda * 2, 64, 128, 2)) return -1; }
+    else       { if (tma::make_2d(&tA, A, K, M, lda * 2, 64, 64, 2)) return -1; }
+    if (!b_mn) { if (tma::make_2d(&tB, B, N, K, ldb * 2, 64, BN / 2, 2)) return -1; }
+    else       { if (tma::make_2d(&tB, B, K, N, ldb * 2, 64, 64, 2)) return -1; }
+    if (!out_f32) { if (tma::make_2d(&tC, Cout, M, N, ldc * 2, 64, 128, 2)) return -1; }
+
+    const int nunits = p.num_m * p.num_n * p.splits;
+    const int grid = 2 * min(nunits, sms / 2);
+    int rc;
+    if (out_f32) rc = BN == 256 ? launch2_major<256, true>(a_mn, b_mn, tA, tB, tC, p, grid, st)
+                                : launch2_major<128, true>(a_mn, b_mn, tA, tB, tC, p, grid, st);
+    else         rc = BN == 256 ? launch2_major<256, false>(a_mn, b_mn, tA, tB, tC, p, grid, st)
+                                : launch2_major<128, false>(a_mn, b_mn, tA, tB, tC, p, grid, st);
+    if (rc) return rc;
+    B200_RETURN_LAUNCH_STATUS("gemm_2cta");
+}

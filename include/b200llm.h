@@ -60,6 +60,10 @@ int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* 
 int b200_gemm_pick_bn(int M, int N, int K, int out_f32);
 int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn_override, int split_k, cudaStream_t st);
 
+/* Same contract on CTA pairs (tcgen05 cta_group::2, cluster of 2): tiles of 256 x bn (bn = 256 | 128), each CTA
+ * stages half of the operands, 6-8 pipeline stages.  The default for large problems. */
+int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn, int split_k, cudaStream_t st);
+
 /* ---- fused AdamW (ref: scripts/train_transformer.py:92,126 torch.optim.AdamW defaults) -------
  * hyper (device, 8 floats) = 1 - lr*weight_decay, beta2, 1 - beta1, 1 - beta2, lr / bias_correction1,
  * sqrt(bias_correction2), eps, grad_scale (derive them in double on the host: ops.adamw_hyper).

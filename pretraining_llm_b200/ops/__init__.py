@@ -40,10 +40,14 @@ def _chk(rc: int, what: str) -> None:
 
 
 # ------------------------------------------------------------------------------------------ GEMM
+GEMM_2CTA = os.environ.get("B200_GEMM_2CTA", "0") == "1"   # flipped to default-on once validated on hardware
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *, a_mn: bool = False,
          b_mn: bool = False, out_dtype=BF16, f32_mode: int = 0, alpha: float = 1.0,
          bias: Optional[torch.Tensor] = None, relu: bool = False, mask: Optional[torch.Tensor] = None,
-         stats: Optional[torch.Tensor] = None, bn: int = 0, split_k: int = 0) -> torch.Tensor:
+         stats: Optional[torch.Tensor] = None, bn: int = 0, split_k: int = 0,
+         two_cta: Optional[bool] = None) -> torch.Tensor:
     """C[M,N] = alpha * opA @ opB^T on the tcgen05 kernel.
 
     a: [M,K] (a_mn=False) or [K,M] (a_mn=True); b: [N,K] (b_mn=False) or [K,N] (b_mn=True); bf16,
@@ -67,9 +71,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     out_f32 = out.dtype == F32
     assert out_f32 or out.dtype == BF16
     L = lib.load()
-    rc = L.b200_gemm(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
-                     int(a_mn), int(b_mn), int(out_f32), f32_mode, float(alpha), _p(bias), int(relu),
-                     _p(mask), 0 if mask is None else mask.stride(0), _p(stats), bn, split_k, _st())
+    if two_cta is None:
+        two_cta = GEMM_2CTA and M >= 512 and N >= 256 and bn in (0, 128, 256)
+    fn = L.b200_gemm_2cta if two_cta else L.b200_gemm
+    if two_cta and bn == 0:
+        bn = 256 if (N % 256 == 0 or N >= 1024) else 128
+    rc = fn(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
+            int(a_mn), int(b_mn), int(out_f32), f32_mode, float(alpha), _p(bias), int(relu),
+            _p(mask), 0 if mask is None else mask.stride(0), _p(stats), bn, split_k, _st())
     _chk(rc, "gemm")
     return out
 

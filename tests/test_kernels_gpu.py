@@ -42,6 +42,32 @@ def test_gemm_tn_bf16(ops, M, N, K, bn):
     assert _rel(c, ref) < 6e-3, _rel(c, ref)
 
 
+@pytest.mark.parametrize("bn", [128, 256])
+@pytest.mark.parametrize("major", ["tn", "nt", "tt"])
+def test_gemm_2cta(ops, bn, major):
+    """cta_group::2 kernel: all operand majors, tails in M / N / K, bf16 and fp32 epilogues."""
+    torch.manual_seed(11)
+    M, N, K = 1000, 712, 328
+    if major == "tn":
+        a, b = _rand(M, K), _rand(N, K)
+        bias = torch.randn(N, device="cuda")
+        c = ops.gemm(a, b, bias=bias, relu=True, bn=bn, two_cta=True)
+        ref = F.relu(a.float() @ b.float().t() + bias)
+        assert _rel(c, ref) < 6e-3, _rel(c, ref)
+    elif major == "nt":
+        a, b = _rand(M, K), _rand(K, N)
+        c = ops.gemm(a, b, b_mn=True, bn=bn, two_cta=True)
+        assert _rel(c, a.float() @ b.float()) < 6e-3
+    else:
+        a, b = _rand(K, M), _rand(K, N)
+        out = torch.zeros(M, N, device="cuda")
+        ops.gemm(a, b, out=out, a_mn=True, b_mn=True, f32_mode=2, split_k=2, bn=bn, two_cta=True)
+        assert _rel(out, a.float().t() @ b.float()) < 2e-3
+    big_a, big_b = _rand(2048, 768), _rand(3072, 768)
+    c = ops.gemm(big_a, big_b, bn=bn, two_cta=True)
+    assert _rel(c, big_a.float() @ big_b.float().t()) < 6e-3
+
+
 def test_gemm_epilogues(ops):
     torch.manual_seed(1)
     M, N, K = 512, 1024, 256

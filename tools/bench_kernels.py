@@ -42,14 +42,17 @@ def gemm_case(name, M, N, K, a_mn=False, b_mn=False, f32=False, **kw):
     a = torch.randn((K, M) if a_mn else (M, K), device="cuda").to(BF16)
     b = torch.randn((K, N) if b_mn else (N, K), device="cuda").to(BF16)
     out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else BF16)
-    ms = timeit(lambda: ops.gemm(a, b, out=out, a_mn=a_mn, b_mn=b_mn, **kw))
+    ms = timeit(lambda: ops.gemm(a, b, out=out, a_mn=a_mn, b_mn=b_mn, two_cta=False, **kw))
+    kw2 = dict(kw); kw2.pop("bn", None)
+    ms2 = timeit(lambda: ops.gemm(a, b, out=out, a_mn=a_mn, b_mn=b_mn, two_cta=True, **kw2))
     A = a.t() if a_mn else a
     Bt = b if b_mn else b.t()
     ref = torch.empty(M, N, device="cuda", dtype=BF16)
     ms_ref = timeit(lambda: torch.matmul(A, Bt, out=ref))
     tf = 2.0 * M * N * K / ms / 1e9
     rows.append(dict(kernel=name, shape=f"{M}x{N}x{K}", ms=round(ms, 4), tflops=round(tf, 1),
-                     frac_of_measured_burst=round(tf / peaks["bf16_tflops"], 3), cublas_ms=round(ms_ref, 4),
+                     frac_of_measured_burst=round(tf / peaks["bf16_tflops"], 3), ms_2cta=round(ms2, 4),
+                     tflops_2cta=round(2.0 * M * N * K / ms2 / 1e9, 1), cublas_ms=round(ms_ref, 4),
                      cublas_tflops=round(2.0 * M * N * K / ms_ref / 1e9, 1)))
     print(rows[-1], flush=True)
 
