@@ -40,7 +40,7 @@ def _chk(rc: int, what: str) -> None:
 
 
 # ------------------------------------------------------------------------------------------ GEMM
-GEMM_2CTA = os.environ.get("B200_GEMM_2CTA", "0") == "1"   # flipped to default-on once validated on hardware
+GEMM_2CTA = os.environ.get("B200_GEMM_2CTA", "1") == "1"   # CTA-pair kernel for large problems (validated on B200)
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *, a_mn: bool = False,
@@ -75,7 +75,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
         two_cta = GEMM_2CTA and M >= 512 and N >= 256 and bn in (0, 128, 256)
     fn = L.b200_gemm_2cta if two_cta else L.b200_gemm
     if two_cta and bn == 0:
-        bn = 256 if (N % 256 == 0 or N >= 1024) else 128
+        bn = 256
+    if two_cta and out_f32 and split_k == 0 and f32_mode in (0, 1):
+        # small weight-gradient outputs with a huge K (tokens): too few 256x256 tiles for the 74 CTA pairs ->
+        # split K in two and combine with fp32 RED (measured best on B200: tools/sweep_wgrad.py)
+        tiles = ((M + 255) // 256) * ((N + bn - 1) // bn)
+        if tiles <= 48 and K >= 2048:
+            if f32_mode == 0:
+                out.zero_()
+            f32_mode, split_k = 2, 2
     rc = fn(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
             int(a_mn), int(b_mn), int(out_f32), f32_mode, float(alpha), _p(bias), int(relu),
             _p(mask), 0 if mask is None else mask.stride(0), _p(stats), bn, split_k, _st())
