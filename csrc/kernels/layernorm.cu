@@ -313,3 +313,65 @@ extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, co
                                                                        accumulate);
     B200_RETURN_LAUNCH_STATUS("ln_bwd");
 }
+
+// =============================================================================================
+// LayerNorm backward for callers that must not allocate.
+//
+// b200_ln_bwd needs a scratch buffer for its per-CTA partial sums and leaves it to the caller to
+// provide one.  Some callers cannot: a C/C++ host that handed the whole device to its own memory
+// arena at start-up has no cudaMalloc left to give (it would fail, or fragment the arena), and a
+// steady-state training loop may refuse cudaMalloc/cudaFree because they synchronise the whole
+// device.  For them the scratch below is part of the library image: a fixed array in device global
+// memory that every GPU loading this library carries until the process exits (6.94 MiB).
+//
+//   * capacity: LN_BWD_STATIC_FLOATS floats = 296 partial rows x 3 accumulators x width 2048.  The
+//     kernel needs  b200_ln_bwd_nparts(M, d) * (colsum ? 3 : 2) * d  floats; bigger requests are
+//     refused with an error, never truncated.
+//   * the array's NAME is only a host-side handle.  Its device address is looked up once per device
+//     with cudaGetSymbolAddress, with that device current, on the first call made on that device;
+//     that first call should therefore happen before any stream capture starts.  Later calls reuse
+//     the cached address and make no CUDA runtime call besides the kernel launches.
+//   * nothing in the array has to be zero on entry: every call overwrites each partial row it later
+//     reads, so the previous call's leftovers are never consumed.
+//   * there is ONE array per GPU.  Two calls whose kernels can overlap on the same GPU (different
+//     streams, or different host threads) race on it; serialise them on one stream.
+// No cudaMalloc, cudaFree or any allocating library routine is called on this path.
+// =============================================================================================
+#define LN_BWD_STATIC_FLOATS (296 * 3 * 2048)
+static __device__ __align__(256) float g_ln_bwd_static_scratch[LN_BWD_STATIC_FLOATS];
+
+static float* ln_bwd_static_address() {
+    static float* addr[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        b200_set_error("ln_bwd_static: cannot identify the current device");
+        return nullptr;
+    }
+    if (addr[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_ln_bwd_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            b200_set_error("ln_bwd_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return nullptr;
+        }
+        addr[dev] = static_cast<float*>(p);
+    }
+    return addr[dev];
+}
+
+extern "C" long long b200_ln_bwd_static_capacity() { return (long long)LN_BWD_STATIC_FLOATS; }
+
+extern "C" int b200_ln_bwd_static(const void* dy, const float* x, const float* mean, const float* rstd,
+                                  const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16, float* dgamma,
+                                  float* dbeta, float* colsum, int M, int d, int accumulate, cudaStream_t st) {
+    const int nparts = b200_ln_bwd_nparts(M, d);
+    B200_REQUIRE(nparts > 0, "ln_bwd_static: unsupported width d=%d", d);
+    const long long need = (long long)nparts * (colsum != nullptr ? 3 : 2) * d;
+    B200_REQUIRE(need <= (long long)LN_BWD_STATIC_FLOATS,
+                 "ln_bwd_static: M=%d d=%d needs %lld floats of scratch but the built-in array holds %lld "
+                 "(use b200_ln_bwd with a caller-provided buffer)", M, d, need, (long long)LN_BWD_STATIC_FLOATS);
+    float* scratch = ln_bwd_static_address();
+    if (scratch == nullptr) return -1;
+    return b200_ln_bwd(dy, x, mean, rstd, gamma, dx_in, dx_out, dx_bf16, scratch, dgamma, dbeta, colsum, M, d, accumulate,
+                       st);
+}

@@ -49,6 +49,15 @@ int b200_ln_bwd_nparts(int M, int d);
  * b200_ln_bwd_nparts(M,d) * (colsum ? 3 : 2) * d floats.  dx_in may alias dx_out. */
 int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16, float* partial, float* dgamma, float* dbeta, float* colsum, int M, int d, int accumulate, cudaStream_t st);
 
+/* Same operation for callers that cannot allocate device memory (a host that gave the whole GPU to its own
+ * arena; a loop that must not meet cudaMalloc's device-wide synchronisation).  This entry point has no
+ * counterpart in the reference.  The partial-sum scratch is a fixed array inside the library image
+ * (b200_ln_bwd_static_capacity() floats = 6.94 MiB held by every GPU that loads the library); requests that
+ * need more are refused.  The first call on a device resolves the array's address (make it before any stream
+ * capture); calls that can overlap on one GPU race on the shared array; nothing needs zeroing between calls. */
+long long b200_ln_bwd_static_capacity(void);
+int b200_ln_bwd_static(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16, float* dgamma, float* dbeta, float* colsum, int M, int d, int accumulate, cudaStream_t st);
+
 /* ---- tcgen05 GEMM (ref: every nn.Linear fwd/bwd: attention.py:47-55, mlp.py:53,66, transformer.py:71)
  * C[M,N] = alpha * opA * opB^T.   a_mn = 0: A is [M,K] (K contiguous); 1: A is [K,M].
  *                                  b_mn = 0: B is [N,K] (K contiguous); 1: B is [K,N].

@@ -129,7 +129,7 @@ def _parse_header():
     text = (INCLUDE / "b200llm.h").read_text()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     sigs = {}
-    for m in re.finditer(r"^\s*(const char\*|int)\s+(b200_\w+)\s*\(([^;]*)\)\s*;", text, flags=re.M):
+    for m in re.finditer(r"^\s*(const char\*|long long|int)\s+(b200_\w+)\s*\(([^;]*)\)\s*;", text, flags=re.M):
         ret, name, args = m.group(1), m.group(2), m.group(3).strip()
         argtypes = []
         if args and args != "void":
@@ -140,7 +140,7 @@ def _parse_header():
                     continue
                 ty = a.replace("const ", "").rsplit(" ", 1)[0].strip()
                 argtypes.append(_CTYPES[ty])
-        sigs[name] = (argtypes, ctypes.c_char_p if "char" in ret else ctypes.c_int)
+        sigs[name] = (argtypes, ctypes.c_char_p if "char" in ret else (ctypes.c_longlong if "long" in ret else ctypes.c_int))
     return sigs
 
 
