@@ -68,11 +68,16 @@ def plan_buckets(layout: ParamLayout, world: int) -> List[BucketPlan]:
 
 
 class DataParallel:
-    def __init__(self, eng, ctx, mode: str = "ddp", ctas: int = 32):
+    def __init__(self, eng, ctx, mode: str = "ddp", ctas: int = 0, ctas_tail: int = 0):
         from .symm import SymmBuffer
         if mode not in ("ddp", "zero"):
             raise ValueError(mode)
-        self.eng, self.ctx, self.mode, self.ctas = eng, ctx, mode, ctas
+        import os
+        # CTAs per reduce kernel.  Measured at W=2 (bench.py, ms/step): 8 -> 23.2, 16 -> 22.0, 32 -> 21.1, 148 -> 20.4:
+        # the kernel is bandwidth/latency bound and co-resides with the GEMM CTAs without slowing them much
+        self.ctas = ctas or int(os.environ.get("B200_DP_CTAS", "148"))
+        self.ctas_tail = ctas_tail or int(os.environ.get("B200_DP_CTAS_TAIL", "148"))
+        self.eng, self.ctx, self.mode = eng, ctx, mode
         self.world, self.rank = ctx.world, ctx.rank
         if self.world not in (1, 2, 4, 8):
             raise ValueError("data-parallel world size must be 1, 2, 4 or 8 (one NVSwitch domain)")
@@ -134,7 +139,7 @@ class DataParallel:
         self.comm_stream.wait_event(ev)
         self._launch(b)
 
-    def _launch(self, b: int) -> None:
+    def _launch(self, b: int, tail: bool = False) -> None:
         start, cnt = self.owned[b]
         end_arr, fp_arr, k = self._slot_arrays[b]
         off = self.opt_off[b]
@@ -143,7 +148,7 @@ class DataParallel:
                                     self.sym_sig.ptr_array, self.world, self.rank, b, self.nb, self.epoch_dev.data_ptr(), start, cnt,
                                     self.m[off:].data_ptr(), self.v[off:].data_ptr(), self.eng.hyper.data_ptr(),
                                     end_arr, fp_arr, k, self.counter[b:].data_ptr(), self.err.data_ptr(),
-                                    self.ctas, self.comm_stream.cuda_stream)
+                                    self.ctas_tail if tail else self.ctas, self.comm_stream.cuda_stream)
         lib.check(rc, "dp_reduce_adamw")
         ops.LAUNCHES += 1
         self._launched.add(b)
@@ -157,7 +162,7 @@ class DataParallel:
         self.comm_stream.wait_event(ev)
         for b in range(self.nb):
             if b not in self._launched:
-                self._launch(b)
+                self._launch(b, tail=True)
         done = torch.cuda.Event()
         done.record(self.comm_stream)
         main.wait_event(done)
