@@ -117,6 +117,11 @@ def run_reference_bench(args, root: str, m: dict, lr: float) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.append(repo)
+    from pretraining_llm_b200.utils.clocks import ClockSampler  # measurement utility only (nvidia-smi reader)
+    clocks = ClockSampler(local, period_ms=100).__enter__()
+
     warm = max(args.warmup, 3)
     try:
         for i in range(warm):
@@ -139,18 +144,17 @@ def run_reference_bench(args, root: str, m: dict, lr: float) -> None:
         for i in range(warm):
             one_step(*staged[i % 4])
 
-    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    sys.path.append(repo)
-    from pretraining_llm_b200.utils.clocks import ClockSampler  # measurement utility only (nvidia-smi reader)
-
     barrier_sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
-        e0.record()
-        for i in range(args.steps):
-            loss = one_step(*staged[i % 4])
-        e1.record()
-        barrier_sync()
+    clocks.mark_start()
+    e0.record()
+    for i in range(args.steps):
+        loss = one_step(*staged[i % 4])
+    e1.record()
+    barrier_sync()
+    clocks.mark_end()
+    time.sleep(0.15)
+    clocks.__exit__(None, None, None)
     ms = max_over_ranks(e0.elapsed_time(e1))
     final_loss = float(loss.item())
     tokens = B * T * world * args.steps

@@ -4,6 +4,7 @@ from __future__ import annotations
 import statistics
 import subprocess
 import threading
+import time
 from typing import List, Optional
 
 _QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -19,7 +20,18 @@ class ClockSampler:
         self.gpu_index, self.period_ms = gpu_index, period_ms
         self.proc: Optional[subprocess.Popen] = None
         self.lines: List[str] = []
+        self.stamps: List[float] = []
+        self.t0: Optional[float] = None
+        self.t1: Optional[float] = None
         self.thread: Optional[threading.Thread] = None
+
+    def mark_start(self) -> None:
+        """Start of the timed region (the sampler itself should be started earlier: nvidia-smi needs a
+        few hundred ms before its first line)."""
+        self.t0 = time.time()
+
+    def mark_end(self) -> None:
+        self.t1 = time.time()
 
     def __enter__(self):
         try:
@@ -33,6 +45,7 @@ class ClockSampler:
         def reader():
             for line in self.proc.stdout:
                 self.lines.append(line.strip())
+                self.stamps.append(time.time())
 
         self.thread = threading.Thread(target=reader, daemon=True)
         self.thread.start()
@@ -50,7 +63,13 @@ class ClockSampler:
     def summary(self) -> dict:
         sm, mx, power = [], [], []
         reasons = set()
-        for ln in self.lines:
+        lines = self.lines
+        if self.t0 is not None:
+            t1 = self.t1 if self.t1 is not None else time.time()
+            inside = [ln for ln, ts in zip(self.lines, self.stamps) if self.t0 <= ts <= t1 + 0.25]
+            if inside:
+                lines = inside
+        for ln in lines:
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 8:
                 continue
