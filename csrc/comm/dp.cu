@@ -91,7 +91,7 @@ template <int W>
 __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int rank, int bucket, int nb, const int* __restrict__ epoch_dev,
                                                               long long start, long long n, float* __restrict__ m,
                                                               float* __restrict__ v, const float* __restrict__ hyper,
-                                                              DpSlots slots, unsigned int* cta_counter, int* err) {
+                                                              DpSlots slots, unsigned int* cta_counter, int* err, int zero_mode) {
     const int epoch = *epoch_dev;   // device-resident step counter: the same CUDA graph serves every step
     // ---- 1. handshake: every rank has finished writing this bucket's gradients
     if (threadIdx.x == 0) {
@@ -141,10 +141,15 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
         }
         const uint2 pb = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
         *reinterpret_cast<float4*>(p_master + e) = pv;
+        if (zero_mode && !need32) {
+            // sharded weights: matrices stay with their owner; consumers pull them inside the forward GEMM
+            *reinterpret_cast<uint2*>(P.wb[rank] + e) = pb;
+        } else {
 #pragma unroll
-        for (int r = 0; r < W; ++r) {
-            *reinterpret_cast<uint2*>(P.wb[r] + e) = pb;
-            if (need32 && r != rank) *reinterpret_cast<float4*>(P.flat[r] + e) = pv;
+            for (int r = 0; r < W; ++r) {
+                *reinterpret_cast<uint2*>(P.wb[r] + e) = pb;
+                if (need32 && r != rank) *reinterpret_cast<float4*>(P.flat[r] + e) = pv;
+            }
         }
     }
     // ---- 5. publish: all CTAs' stores are visible before the done flag goes up
@@ -170,7 +175,7 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
                                     int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start,
                                     long long n, float* m, float* v, const float* hyper, const long long* h_slot_end,
                                     const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas,
-                                    cudaStream_t st) {
+                                    int zero_mode, cudaStream_t st) {
     B200_REQUIRE(world >= 1 && world <= DP_MAX_WORLD, "dp: world size %d not supported (max %d)", world, DP_MAX_WORLD);
     B200_REQUIRE(n_slots <= DP_MAX_SLOTS, "dp: too many slots in one bucket");
     B200_REQUIRE(n % 4 == 0 && start % 4 == 0, "dp: slice must be 16-byte aligned");
@@ -186,7 +191,7 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
     for (int k = 0; k < n_slots; ++k) { S.end[k] = h_slot_end[k]; S.fp32[k] = h_slot_fp32[k]; }
 #define DP_LAUNCH(W_)                                                                                            \
     dp_reduce_adamw_kernel<W_><<<ctas, 512, 0, st>>>(P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
-                                                     (unsigned int*)cta_counter, err)
+                                                     (unsigned int*)cta_counter, err, zero_mode)
     switch (world) {
         case 1: DP_LAUNCH(1); break;
         case 2: DP_LAUNCH(2); break;

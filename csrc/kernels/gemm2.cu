@@ -21,6 +21,7 @@
 namespace {
 
 using gemm::Params;
+using gemm::AgParams;
 using gemm::EPI_BUF_BYTES;
 constexpr int BK = 64;
 constexpr int A_BYTES = 128 * BK * 2;   // this CTA's 128 rows of A
@@ -34,10 +35,21 @@ template <int BN> struct Cfg2 {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * EPI_BUF_BYTES + 256 + 1024 + 1024;
 };
 
-template <int BN, bool A_MN, bool B_MN, bool OUT_F32>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// AG = true: 4 extra warps (6..9) pull the remote chunks of the layer's weights over NVLink into the local
+// buffer while the tiles whose weights are already local run; the TMA producer waits per chunk.
+template <int BN, bool A_MN, bool B_MN, bool OUT_F32, bool AG>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(AG ? NUM_THREADS + 128 : NUM_THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-             const __grid_constant__ CUtensorMap tmC, const Params p) {
+             const __grid_constant__ CUtensorMap tmC, const Params p, const AgParams ag) {
     using C = Cfg2<BN>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -89,12 +101,28 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            unsigned ready_mask = 0;                    // chunks already seen valid (AG)
+            const int ag_epoch = (AG && ag.flags != nullptr) ? *ag.epoch : 0;
             for (int u = pair; u < nunits; u += npairs) {
                 const int tile = u % ntiles, split = u / ntiles;
                 const int m0 = (tile % p.num_m) * 256 + (int)rank * 128;
-                const int n0 = (tile / p.num_m) * BN + (int)rank * (BN / 2);
+                const int n0 = (((tile / p.num_m) + p.n_shift) % p.num_n) * BN + (int)rank * (BN / 2);
                 const int kb0 = split * p.kb_per_split;
                 const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+                if (AG && ag.flags != nullptr && !B_MN) {
+                    // rows [n0, n0 + BN/2) of the [N, K] weight -> flat element range -> owning chunks
+                    const long long e0 = ag.w_offset + (long long)min(n0, p.N) * p.K;
+                    const long long e1 = ag.w_offset + (long long)min(n0 + BN / 2, p.N) * p.K;
+                    if (e1 > e0) {
+                        const int c0 = (int)((e0 - ag.layer_start) / ag.chunk), c1 = (int)((e1 - 1 - ag.layer_start) / ag.chunk);
+                        for (int c = c0; c <= c1; ++c) {
+                            if (c == ag.rank || (ready_mask >> c) & 1u) continue;
+                            while (ld_acquire_gpu(ag.flags + c) < ag_epoch) __nanosleep(32);
+                            ready_mask |= 1u << c;
+                        }
+                        asm volatile("fence.proxy.async;" ::: "memory");   // gathered by generic stores, read by TMA
+                    }
+                }
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(empty_bar(stage), phase ^ 1);
                     if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
@@ -155,7 +183,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
-    } else {
+    } else if (warp < 6) {
         // ------------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
         const int q = warp & 3;
         const int row = q * 32 + lane;
@@ -165,7 +193,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         int buf = 0;
         for (int u = pair; u < nunits; u += npairs) {
             const int tile = u % ntiles;
-            const int n_blk = tile / p.num_m;
+            const int n_blk = ((tile / p.num_m) + p.n_shift) % p.num_n;
             const int m0 = (tile % p.num_m) * 256 + (int)rank * 128, n0 = n_blk * BN;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
             const uint32_t te = ptx::mapa(tempty_bar(acc), 0);   // the leader's accumulator-empty barrier
@@ -175,6 +203,41 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (!OUT_F32 && store_thread) ptx::tma_store_wait_all<0>();
+    } else if (AG) {
+        // ------------------------------------------------------------------ gather warps (6..9, every CTA)
+        if (ag.gather) {
+            const int gt = (int)threadIdx.x - NUM_THREADS;              // 0..127
+            const int epoch = *ag.epoch;
+            bf16* dst = ag.wb[ag.rank];
+            for (int s = 1; s < ag.world; ++s) {
+                const int src_rank = (ag.rank + s) % ag.world;
+                const long long c_lo = ag.layer_start + (long long)src_rank * ag.chunk;
+                const long long c_hi = c_lo + ag.chunk < ag.layer_end ? c_lo + ag.chunk : ag.layer_end;
+                const bf16* src = ag.wb[src_rank];
+                // 16-byte vectors, 4 loads in flight per thread, grid-strided over all CTAs' gather threads
+                const long long nvec = c_hi > c_lo ? (c_hi - c_lo) / 8 : 0;
+                const uint4* sv = reinterpret_cast<const uint4*>(src + c_lo);
+                uint4* dv = reinterpret_cast<uint4*>(dst + c_lo);
+                const long long stride = (long long)gridDim.x * 128;
+                long long i = (long long)blockIdx.x * 128 + gt;
+                for (; i + 3 * stride < nvec; i += 4 * stride) {
+                    const uint4 a = ldg_stream_u4(sv + i), b = ldg_stream_u4(sv + i + stride),
+                                c = ldg_stream_u4(sv + i + 2 * stride), d = ldg_stream_u4(sv + i + 3 * stride);
+                    dv[i] = a; dv[i + stride] = b; dv[i + 2 * stride] = c; dv[i + 3 * stride] = d;
+                }
+                for (; i < nvec; i += stride) dv[i] = ldg_stream_u4(sv + i);
+                __threadfence();
+                asm volatile("bar.sync 2, 128;" ::: "memory");
+                if (gt == 0) {
+                    const unsigned prev = atomicAdd(ag.counters + src_rank, 1u);
+                    if (prev == gridDim.x - 1) {
+                        ag.counters[src_rank] = 0;
+                        __threadfence();
+                        st_release_gpu(ag.flags_w + src_rank, epoch);
+                    }
+                }
+            }
+        }
     }
 
     ptx::tc_fence_before();
@@ -185,15 +248,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool OUT_F32>
-int launch2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const Params& p, int grid, cudaStream_t st) {
-    auto kern = gemm2_kernel<BN, A_MN, B_MN, OUT_F32>;
+template <int BN, bool A_MN, bool B_MN, bool OUT_F32, bool AG = false>
+int launch2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const Params& p, int grid, cudaStream_t st,
+            const AgParams* ag = nullptr) {
+    auto kern = gemm2_kernel<BN, A_MN, B_MN, OUT_F32, AG>;
     static bool configured = false;
     if (!configured) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::SMEM_BYTES));
         configured = true;
     }
-    kern<<<grid, NUM_THREADS, Cfg2<BN>::SMEM_BYTES, st>>>(tA, tB, tC, p);
+    AgParams none;
+    memset(&none, 0, sizeof(none));
+    kern<<<grid, AG ? NUM_THREADS + 128 : NUM_THREADS, Cfg2<BN>::SMEM_BYTES, st>>>(tA, tB, tC, p, ag ? *ag : none);
     return 0;
 }
 
@@ -256,4 +322,46 @@ extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, i
                                 : launch2_major<128, false>(a_mn, b_mn, tA, tB, tC, p, grid, st);
     if (rc) return rc;
     B200_RETURN_LAUNCH_STATUS("gemm_2cta");
+}
+
+// All-gather fused forward GEMM for sharded data parallelism: C = A * W^T (+bias, ReLU) where W [N, K] is a slot
+// of the flat bf16 weight buffer at element offset w_offset, inside a layer range [layer_start, layer_end) whose
+// `world` chunks are owned by the ranks.  flags/counters: [world] ints (local, zero-initialised once).
+// gather != 0: this launch also pulls every remote chunk of the layer from h_wb[peer] into h_wb[rank]
+// (the first weight-consuming GEMM of the layer); later GEMMs of the layer only wait on the flags.
+extern "C" int b200_gemm_ag(const void* A, void* Cout, int M, int N, int K, long long lda, long long ldc, const float* bias,
+                            int relu, void* const* h_wb, int world, int rank, long long layer_start, long long layer_end,
+                            long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev,
+                            int gather, cudaStream_t st) {
+    B200_REQUIRE(world >= 1 && world <= 8, "gemm_ag: world size %d not supported", world);
+    B200_REQUIRE(M > 0 && N > 0 && K > 0 && lda % 8 == 0 && ldc % 8 == 0 && K % 8 == 0, "gemm_ag: bad shape / alignment");
+    B200_REQUIRE(layer_start % 8 == 0 && chunk % 8 == 0 && w_offset % 8 == 0, "gemm_ag: offsets must be multiples of 8");
+    constexpr int BN = 256;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = N; p.K = K;
+    p.num_m = (M + 255) / 256;
+    p.num_n = (N + BN - 1) / BN;
+    p.num_kb = (K + BK - 1) / BK;
+    p.splits = 1; p.kb_per_split = p.num_kb;
+    p.alpha = 1.f; p.bias = bias; p.relu = relu;
+    // start with the n-tiles whose weight rows this rank owns
+    const long long own = layer_start + (long long)rank * chunk - w_offset;
+    if (own > 0 && own < (long long)N * K) p.n_shift = (int)(((own + K - 1) / K + BN - 1) / BN) % p.num_n;
+    AgParams ag;
+    memset(&ag, 0, sizeof(ag));
+    ag.flags = flags; ag.flags_w = flags; ag.epoch = epoch_dev; ag.layer_start = layer_start; ag.layer_end = layer_end;
+    ag.chunk = chunk; ag.w_offset = w_offset; ag.world = world; ag.rank = rank; ag.gather = gather;
+    ag.counters = (unsigned int*)counters;
+    for (int r = 0; r < world; ++r) ag.wb[r] = (bf16*)h_wb[r];
+    const bf16* W = (const bf16*)h_wb[rank] + w_offset;
+    CUtensorMap tA, tB, tC;
+    if (tma::make_2d(&tA, A, M, K, lda * 2, 64, 128, 2)) return -1;
+    if (tma::make_2d(&tB, W, N, K, (uint64_t)K * 2, 64, BN / 2, 2)) return -1;
+    if (tma::make_2d(&tC, Cout, M, N, ldc * 2, 64, 128, 2)) return -1;
+    const int sms = b200_num_sms();
+    const int nunits = p.num_m * p.num_n;
+    const int grid = 2 * min(nunits, sms / 2);
+    if (launch2<BN, false, false, false, true>(tA, tB, tC, p, grid, st, &ag)) return -1;
+    B200_RETURN_LAUNCH_STATUS("gemm_ag");
 }

@@ -26,6 +26,24 @@ struct Params {
     float* out_f32;
     long long ldc;
     int f32_mode;           // 0 store, 1 accumulate (+=), 2 atomic add
+    int n_shift;            // rotate the n-tile order (all-gather fused GEMM: start with the locally owned rows)
+};
+
+// All-gather fused into the GEMM (sharded data parallelism): the B operand (a weight matrix) lives in a flat
+// bf16 buffer whose layer range [layer_start, layer_end) is split in `world` contiguous chunks, chunk c owned
+// (kept up to date) by rank c.  flags[c] >= *epoch means chunk c of this layer is valid in the LOCAL buffer.
+struct AgParams {
+    const int* flags;         // [world] local "chunk gathered" flags of this layer (null: feature off)
+    const int* epoch;         // device step counter
+    long long layer_start;    // element offsets in the flat bf16 weight buffer
+    long long layer_end;
+    long long chunk;          // elements per rank
+    long long w_offset;       // first element of this GEMM's weight matrix
+    int world, rank;
+    int gather;               // 1: this launch also PULLS the layer's remote chunks (first consumer GEMM of the layer)
+    bf16* wb[8];              // peer-mapped flat bf16 weight buffers (index = rank; own buffer included)
+    int* flags_w;             // same flags, writable
+    unsigned int* counters;   // [world] zero-initialised arrival counters
 };
 
 // tfull_bar: local mbarrier (shared::cta address) the MMA issuer commits to; taddr: TMEM address of this

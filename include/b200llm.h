@@ -73,6 +73,14 @@ int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long l
  * stages half of the operands, 6-8 pipeline stages.  The default for large problems. */
 int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn, int split_k, cudaStream_t st);
 
+/* All-gather fused into the forward GEMM (sharded data parallelism, ref: absent in the reference - SURVEY N6/T11):
+ * C[M,N] = A[M,K] * W^T (+bias) (ReLU), W [N,K] = a slot of the flat bf16 weight buffer at element w_offset inside
+ * a layer range [layer_start, layer_end) whose `world` equal chunks are owned by the ranks.  h_wb: host array of the
+ * peer-mapped flat weight buffers.  flags / counters: [world] ints on this device, zero-initialised once.
+ * gather != 0: this launch's extra warps pull every remote chunk of the layer over NVLink into the local buffer and
+ * raise flags[c] = *epoch_dev; tiles whose rows are already local run meanwhile, the others wait per chunk. */
+int b200_gemm_ag(const void* A, void* C, int M, int N, int K, long long lda, long long ldc, const float* bias, int relu, void* const* h_wb, int world, int rank, long long layer_start, long long layer_end, long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev, int gather, cudaStream_t st);
+
 /* ---- fused AdamW (ref: scripts/train_transformer.py:92,126 torch.optim.AdamW defaults) -------
  * hyper (device, 8 floats) = 1 - lr*weight_decay, beta2, 1 - beta1, 1 - beta2, lr / bias_correction1,
  * sqrt(bias_correction2), eps, grad_scale (derive them in double on the host: ops.adamw_hyper).
@@ -132,8 +140,9 @@ int b200_ipc_close(void* ptr);
  * sig: int[2][world][num_buckets] per rank (ready | done), zero-initialised; *epoch_dev: 1, 2, 3, ...
  * (a device int the caller increments once per step, so a captured graph can be replayed);
  * m, v: this rank's moments for the slice; h_slot_end / h_slot_fp32: element end offsets and
- * "consumers read fp32" flags of the parameter slots inside the bucket. */
-int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start, long long n, float* m, float* v, const float* hyper, const long long* h_slot_end, const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas, cudaStream_t st);
+ * "consumers read fp32" flags of the parameter slots inside the bucket.  zero_mode != 0: bf16-only slots
+ * (weight matrices) are NOT pushed to the peers - they stay sharded and are pulled by b200_gemm_ag. */
+int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start, long long n, float* m, float* v, const float* hyper, const long long* h_slot_end, const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas, int zero_mode, cudaStream_t st);
 /* blocks the stream until every owner's done flag of every bucket has reached `epoch` */
 int b200_dp_wait_done(const int* sig, int world, int num_buckets, const int* epoch_dev, int* err, cudaStream_t st);
 

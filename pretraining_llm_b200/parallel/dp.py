@@ -117,6 +117,12 @@ class DataParallel:
             off += cnt
         if eng.exp_avg is not None:
             self.state_loaded()
+        # sharded-weight ("zero") mode: per-layer, per-source-rank "chunk gathered" flags + arrival counters, and the
+        # weight version they are compared against (bumped after every optimizer step)
+        self.zero = mode == "zero"
+        self.ag_flags = torch.zeros(max(lay.L, 1), self.world, device=dev, dtype=torch.int32)
+        self.ag_counters = torch.zeros(max(lay.L, 1), self.world, device=dev, dtype=torch.int32)
+        self.version_dev = torch.zeros(1, device=dev, dtype=torch.int32)
         self.counter = torch.zeros(self.nb, device=dev, dtype=torch.int32)
         self.err = torch.zeros(1, device=dev, dtype=torch.int32)
         self.epoch_dev = torch.zeros(1, device=dev, dtype=torch.int32)   # incremented on the device each step
@@ -148,7 +154,9 @@ class DataParallel:
                                     self.sym_sig.ptr_array, self.world, self.rank, b, self.nb, self.epoch_dev.data_ptr(), start, cnt,
                                     self.m[off:].data_ptr(), self.v[off:].data_ptr(), self.eng.hyper.data_ptr(),
                                     end_arr, fp_arr, k, self.counter[b:].data_ptr(), self.err.data_ptr(),
-                                    self.ctas_tail if tail else self.ctas, self.comm_stream.cuda_stream)
+                                    self.ctas_tail if tail else self.ctas,
+                                    1 if (self.zero and self.plans[b].name.startswith("block")) else 0,
+                                    self.comm_stream.cuda_stream)
         lib.check(rc, "dp_reduce_adamw")
         ops.LAUNCHES += 1
         self._launched.add(b)
@@ -170,7 +178,48 @@ class DataParallel:
                                           self.epoch_dev.data_ptr(), self.err.data_ptr(), main.cuda_stream)
         lib.check(rc, "dp_wait_done")
         ops.LAUNCHES += 1
+        if self.zero:
+            ops.incr_int(self.version_dev, 1)            # the sharded matrices changed: next forward re-gathers
         self._launched = set()
+
+    # ------------------------------------------------------------------ sharded weights ("zero" mode)
+    def gemm_ag(self, layer: int, slot_name: str, a: torch.Tensor, out: torch.Tensor, bias=None, relu: bool = False,
+                gather: bool = False) -> None:
+        """Forward GEMM of a block whose weight matrix is sharded across the ranks: the all-gather of the layer's
+        weights is fused into the (first) GEMM that consumes them (csrc/kernels/gemm2.cu, b200_gemm_ag)."""
+        lay = self.eng.layout
+        plan = self.plans[self.index[f"block{layer}"]]
+        slot = lay.slots[slot_name]
+        N, K = slot.shape
+        M = a.shape[0]
+        rc = lib.load().b200_gemm_ag(a.data_ptr(), out.data_ptr(), M, N, K, a.stride(0), out.stride(0),
+                                     None if bias is None else bias.data_ptr(), int(relu), self.sym_wb.ptr_array,
+                                     self.world, self.rank, plan.start, plan.end, plan.chunk, slot.offset,
+                                     self.ag_flags[layer].data_ptr(), self.ag_counters[layer].data_ptr(),
+                                     self.version_dev.data_ptr(), int(gather), torch.cuda.current_stream().cuda_stream)
+        lib.check(rc, "gemm_ag")
+        ops.LAUNCHES += 1
+
+    def gather_weights(self) -> None:
+        """Bring every remote chunk of every block into the local bf16 shadow with plain peer copies (used off the
+        hot path: before generation / evaluation with small shapes, where the GEMMs are not the AG kind)."""
+        if not self.zero:
+            return
+        from .symm import _CudaArray
+        n = self.eng.layout.total
+        torch.cuda.synchronize()
+        dist.barrier()
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            peer = torch.as_tensor(_CudaArray(self.sym_wb.ptrs[r], n * 2), device=self.eng.device).view(BF16)
+            for p in self.plans:
+                if p.name.startswith("block"):
+                    s, c = p.slice_of(r)
+                    self.eng.wb[s:s + c].copy_(peer[s:s + c])
+        self.ag_flags.fill_(int(self.version_dev.item()))
+        torch.cuda.synchronize()
+        dist.barrier()
 
     def begin_step(self) -> None:
         """First thing of a step (main stream): advance the device-side epoch."""

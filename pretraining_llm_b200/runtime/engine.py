@@ -157,15 +157,24 @@ class Engine:
                 sp = (l - 1) if w.train else 0
                 ops.ln_fwd(w.resid_b[sp], self.P(pre + "ln1.weight"), self.P(pre + "ln1.bias"), branch=w.mlp_out,
                            x_out=ra_in, out=w.h1[s], mean=st1[0], rstd=st1[1])
-            ops.gemm(w.h1[s], self.W(pre + "attn.wqkv"), out=w.qkv[s])
+            zero = self.dp is not None and self.dp.zero and w.M >= 512
+            if zero:   # sharded weights: all-gather of the layer fused into its first GEMM
+                self.dp.gemm_ag(l, pre + "attn.wqkv", w.h1[s], w.qkv[s], gather=True)
+            else:
+                ops.gemm(w.h1[s], self.W(pre + "attn.wqkv"), out=w.qkv[s])
             if kv is not None:
                 ops.kv_append(w.qkv[s], kv[0][l], kv[1][l], B, T, H, hs, kv[0].shape[3], pos0=pos0)
             ops.attn_fwd(w.qkv[s], B, T, H, hs, out=w.att[s], lse=w.lse[s])
             ops.ln_fwd(ra_in, self.P(pre + "ln2.weight"), self.P(pre + "ln2.bias"), branch=w.att[s],
                        x_out=w.resid_b[s], out=w.h2[s], mean=st2[0], rstd=st2[1])
-            ops.gemm(w.h2[s], self.W(pre + "mlp.hidden.weight"), out=w.act[s], bias=self.P(pre + "mlp.hidden.bias"),
-                     relu=True)
-            ops.gemm(w.act[s], self.W(pre + "mlp.proj.weight"), out=w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
+            if zero:
+                self.dp.gemm_ag(l, pre + "mlp.hidden.weight", w.h2[s], w.act[s], bias=self.P(pre + "mlp.hidden.bias"),
+                                relu=True)
+                self.dp.gemm_ag(l, pre + "mlp.proj.weight", w.act[s], w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
+            else:
+                ops.gemm(w.h2[s], self.W(pre + "mlp.hidden.weight"), out=w.act[s],
+                         bias=self.P(pre + "mlp.hidden.bias"), relu=True)
+                ops.gemm(w.act[s], self.W(pre + "mlp.proj.weight"), out=w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
         sl = (L - 1) if w.train else 0
         sf = L if w.train else 1
         stf = w.ln_stats[2 * (L if w.train else 1)]
@@ -332,6 +341,8 @@ class Engine:
     # ------------------------------------------------------------------ generation
     def generate(self, idx, max_new_tokens, **kw):
         from .generation import Generator
+        if self.dp is not None:
+            self.dp.gather_weights()          # sharded mode: small-shape GEMMs read the local shadow
         if self._gen is None:
             self._gen = Generator(self)
         return self._gen.generate(idx, max_new_tokens, **kw)

@@ -37,7 +37,7 @@ def main():
         torch.manual_seed(0)
         oracle = Transformer(**CFG, N_BLOCKS=L).to(ctx.device)
     eng = model.engine
-    eng.dp = DataParallel(eng, ctx)
+    eng.dp = DataParallel(eng, ctx, mode=os.environ.get("DP_MODE", "ddp"))
     losses = []
     for step in range(STEPS):
         x, y = batches(r, step)
@@ -50,6 +50,7 @@ def main():
     mean_loss = torch.stack(losses).clone()
     dist.all_reduce(mean_loss)
     mean_loss /= W
+    eng.dp.gather_weights()                      # no-op in ddp mode
     # (2) bf16 replicas identical
     wb = eng.wb.clone()
     ref = wb.clone()
