@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--dp-mode", default="ddp", choices=["ddp", "zero"])
+    ap.add_argument("--vocab-parallel", action="store_true")
     return ap.parse_args()
 
 
@@ -124,7 +125,7 @@ def run_ours(args):
     if world > 1:
         from pretraining_llm_b200.parallel.dp import DataParallel
         ctx = DistContext(rank=rank, local_rank=local, world=world, device=dev)
-        eng.dp = DataParallel(eng, ctx, mode=args.dp_mode)
+        eng.dp = DataParallel(eng, ctx, mode=args.dp_mode, vocab_parallel=args.vocab_parallel)
         mode = "fused-allreduce-adamw" if args.dp_mode == "ddp" else "zero: fused reduce-scatter+adamw, all-gather fused in GEMMs"
     batches = synthetic_batches(4, B, T, V, dev, seed=100 + rank)
     use_graph = not args.no_graph

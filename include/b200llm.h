@@ -146,6 +146,18 @@ int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_
 /* blocks the stream until every owner's done flag of every bucket has reached `epoch` */
 int b200_dp_wait_done(const int* sig, int world, int num_buckets, const int* epoch_dev, int* err, cudaStream_t st);
 
+/* ---- vocab-parallel LM head + cross-entropy (ref: replicated lm_head + F.cross_entropy, transformer.py:71-77)
+ * Every rank owns Vs consecutive vocabulary rows.  All h_* arguments are host arrays of `world` peer-mapped device
+ * pointers; h_sig: signal pads int[4][world]; `slot` selects the hand-shake; *epoch_dev is the device step counter.
+ * gather_rows : dst_all[src*M + i, :] = hf[src][i, :], tgt_all[src*M + i] = tgt[src][i] - tgt_shift
+ * ce_finalize : for this rank's M rows, combine stats (float2 [nt_local][world*M]) of all slices, fetch the target
+ *               logit from its owner's logits [world*M, ldl], loss_sum += sum_scale * sum, push lse to every rank
+ * reduce_rows : out[i, :] = scale * sum_src partial[src][rank*M + i, :]   (bf16) */
+int b200_vp_barrier(void* const* h_sig, int world, int rank, int slot, const int* epoch_dev, int* err, cudaStream_t st);
+int b200_vp_gather_rows(void* const* h_hf, void* const* h_tgt, void* dst_all, long long* tgt_all, int M, int d, int world, int rank, long long tgt_shift, void* const* h_sig, int slot, const int* epoch_dev, int* err, cudaStream_t st);
+int b200_vp_ce_finalize(void* const* h_stats, void* const* h_logits, void* const* h_lse_all, const long long* targets, float* loss_sum, float* loss_rows, int M, int world, int rank, int V, int Vs, int nt_local, long long ldl, float sum_scale, void* const* h_sig, int slot, const int* epoch_dev, int* err, cudaStream_t st);
+int b200_vp_reduce_rows(void* const* h_partial, void* out, int M, int d, int world, int rank, float scale, void* const* h_sig, int slot, const int* epoch_dev, int* err, cudaStream_t st);
+
 #ifdef __cplusplus
 }
 #endif

@@ -70,6 +70,7 @@ default_config = {
     "seed": 1337,
     "grad_accum_steps": 1,
     "dp_mode": "ddp",            # "ddp" (replicated bf16 weights) | "zero" (sharded)
+    "vocab_parallel": False,     # multi-GPU: shard the LM head + cross-entropy over the vocabulary
     "lr_schedule": "reference",  # "reference" = warm-up then constant (train_transformer.py:43-49)
                                  # "decay"     = additionally honour t_lr_decay_step / t_lr_decayed
     "synthetic_data": False,     # True: random tokens of the right shape, no files needed

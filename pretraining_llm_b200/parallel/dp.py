@@ -49,11 +49,15 @@ class BucketPlan:
         return s, e - s
 
 
-def plan_buckets(layout: ParamLayout, world: int) -> List[BucketPlan]:
-    """Static ownership map: bucket b's elements [start + r*chunk, start + (r+1)*chunk) belong to rank r."""
+def plan_buckets(layout: ParamLayout, world: int, vocab_parallel: bool = False) -> List[BucketPlan]:
+    """Static ownership map: bucket b's elements [start + r*chunk, start + (r+1)*chunk) belong to rank r.
+    With a vocab-parallel LM head, lm_head.weight / lm_head.bias are owned by vocabulary slice instead
+    (parallel/vp.py) and leave the head bucket."""
     slots = list(layout.slots.values())
     plans = []
     for name, start, end in layout.buckets():
+        if vocab_parallel and name == "head":
+            end = layout.slots["lm_head.weight"].offset
         n = end - start
         chunk = (n + world - 1) // world
         chunk = (chunk + 3) // 4 * 4
@@ -68,7 +72,7 @@ def plan_buckets(layout: ParamLayout, world: int) -> List[BucketPlan]:
 
 
 class DataParallel:
-    def __init__(self, eng, ctx, mode: str = "ddp", ctas: int = 0, ctas_tail: int = 0):
+    def __init__(self, eng, ctx, mode: str = "ddp", ctas: int = 0, ctas_tail: int = 0, vocab_parallel: bool = False):
         from .symm import SymmBuffer
         if mode not in ("ddp", "zero"):
             raise ValueError(mode)
@@ -84,7 +88,7 @@ class DataParallel:
         lay: ParamLayout = eng.layout
         dev = eng.device
         n = lay.total
-        self.plans = plan_buckets(lay, self.world)
+        self.plans = plan_buckets(lay, self.world, vocab_parallel)
         self.nb = len(self.plans)
         self.index: Dict[str, int] = {p.name: i for i, p in enumerate(self.plans)}
         # ---- symmetric buffers: gradients, bf16 weights, fp32 masters, signal pad
@@ -132,6 +136,10 @@ class DataParallel:
         for p in self.plans:
             k = len(p.slot_end)
             self._slot_arrays.append(((ctypes.c_longlong * k)(*p.slot_end), (ctypes.c_int * k)(*p.slot_fp32), k))
+        self.vp = None
+        if vocab_parallel and self.world > 1:
+            from .vp import VocabParallelHead
+            self.vp = VocabParallelHead(eng, self)
         dist.barrier()
         torch.cuda.synchronize()
 
@@ -203,6 +211,8 @@ class DataParallel:
     def gather_weights(self) -> None:
         """Bring every remote chunk of every block into the local bf16 shadow with plain peer copies (used off the
         hot path: before generation / evaluation with small shapes, where the GEMMs are not the AG kind)."""
+        if self.vp is not None:
+            self.vp.gather_full(with_moments=False)
         if not self.zero:
             return
         from .symm import _CudaArray
@@ -250,11 +260,15 @@ class DataParallel:
         eng.ensure_opt_state()
         self._gather([self.m[o:o + c] for o, (_, c) in zip(self.opt_off, self.owned)], eng.exp_avg)
         self._gather([self.v[o:o + c] for o, (_, c) in zip(self.opt_off, self.owned)], eng.exp_avg_sq)
+        if self.vp is not None:
+            self.vp.gather_full(with_moments=True)
         eng._wb_version = eng.flat._version
 
     def state_loaded(self) -> None:
         """Full moments were loaded into eng.exp_avg(_sq) (resume): keep the owned slices."""
         eng = self.eng
+        if getattr(self, "vp", None) is not None:
+            self.vp.state_loaded()
         for o, (s, c) in zip(self.opt_off, self.owned):
             self.m[o:o + c] = eng.exp_avg[s:s + c]
             self.v[o:o + c] = eng.exp_avg_sq[s:s + c]

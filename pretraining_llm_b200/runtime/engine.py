@@ -204,6 +204,9 @@ class Engine:
         ops.embed_fwd(w.idx, self.P("token_embed.weight"), self.P("position_embed.weight"), out=w.resid_a[0])
         self._blocks_forward(w)
         V = lay.V
+        if with_loss and w.train and self.dp is not None and self.dp.vp is not None:
+            self.dp.vp.forward(w, loss_scale)      # vocab-parallel LM head + CE across the ranks
+            return
         ops.gemm(w.hf, self.W("lm_head.weight"), out=w.logits[:, :V], bias=self.P("lm_head.bias"),
                  stats=w.ce_stats if with_loss else None, bn=256)
         if with_loss:
@@ -227,10 +230,13 @@ class Engine:
         if not accumulate:
             self.G("token_embed.weight").zero_()     # scatter-add target
         # LM head + CE
-        dlog = w.logits[:, :V]
-        ops.ce_grad(dlog, w.ce_lse, w.tgt.view(-1), self.G("lm_head.bias"), V, grad_scale / M, accumulate=accumulate)
-        ops.gemm(dlog, w.hf, out=self.G("lm_head.weight"), a_mn=True, b_mn=True, f32_mode=fm)
-        ops.gemm(dlog, self.W("lm_head.weight"), out=w.dtmp, b_mn=True)
+        if self.dp is not None and self.dp.vp is not None:
+            self.dp.vp.backward(w, grad_scale, accumulate)
+        else:
+            dlog = w.logits[:, :V]
+            ops.ce_grad(dlog, w.ce_lse, w.tgt.view(-1), self.G("lm_head.bias"), V, grad_scale / M, accumulate=accumulate)
+            ops.gemm(dlog, w.hf, out=self.G("lm_head.weight"), a_mn=True, b_mn=True, f32_mode=fm)
+            ops.gemm(dlog, self.W("lm_head.weight"), out=w.dtmp, b_mn=True)
         stf = w.ln_stats[2 * L]
         ops.ln_bwd(w.dtmp, w.resid_a[L], stf[0], stf[1], self.P("layer_norm.weight"), self.G("layer_norm.weight"),
                    self.G("layer_norm.bias"), dx_out=w.dx, dx_bf16=w.dx_bf16, partial=w.ln_partial, accumulate=accumulate)
@@ -267,6 +273,9 @@ class Engine:
     def set_hyper(self, lr: float, grad_scale: float = 1.0) -> None:
         """Stage AdamW scalars for the NEXT optimizer launch (also read by graph replays)."""
         self.step_count += 1
+        if self.dp is not None and self.dp.vp is not None:
+            self.dp.vp.set_hyper(ops.adamw_hyper(lr, self.step_count, self.betas[0], self.betas[1], self.eps,
+                                                 self.weight_decay, grad_scale))
         if self.dp is not None:
             grad_scale = grad_scale / self.dp.world       # average of the per-rank mean losses
         vals = ops.adamw_hyper(lr, self.step_count, self.betas[0], self.betas[1], self.eps, self.weight_decay,
@@ -280,6 +289,8 @@ class Engine:
         self.ensure_opt_state()
         if self.dp is not None:
             self.dp.reduce_and_step()
+            if self.dp.vp is not None:
+                self.dp.vp.step()
         else:
             ops.adamw(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.wb, self.hyper)
         # our kernel wrote the masters and the shadow together: keep them marked in sync

@@ -56,7 +56,8 @@ class Trainer:
         self.log_file = open(self.config["log_jsonl"], "a") if self.config.get("log_jsonl") and self.dist.master else None
         if self.native and self.dist.world > 1:
             from ..parallel.dp import DataParallel
-            model.engine.dp = DataParallel(model.engine, self.dist, mode=self.config.get("dp_mode", "ddp"))
+            model.engine.dp = DataParallel(model.engine, self.dist, mode=self.config.get("dp_mode", "ddp"),
+                                           vocab_parallel=bool(self.config.get("vocab_parallel", False)))
 
     # reference-compatible private names
     def _get_lr(self, it: int) -> float:
@@ -73,6 +74,8 @@ class Trainer:
         if self.val_iterator is None:
             return float("nan")
         self.model.eval()
+        if self.native and self.model.engine.dp is not None:
+            self.model.engine.dp.gather_weights()      # sharded / vocab-parallel weights -> complete local copy
         n = self.config["t_eval_iters"]
         total = torch.zeros((), device=next(self.model.parameters()).device)
         for _ in range(n):

@@ -11,11 +11,15 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+@pytest.mark.parametrize("mode", ["ddp", "zero", "ddp+vp"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_fused_dp_matches_single_gpu(world):
+def test_fused_dp_matches_single_gpu(world, mode):
+    """ddp: push-based weight broadcast; zero: sharded matrices, all-gather fused into the forward GEMMs;
+    +vp: vocab-parallel LM head + cross-entropy.  All must reproduce the single-GPU oracle."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
+    env = dict(os.environ, DP_MODE=mode.split("+")[0], DP_VP="1" if "vp" in mode else "0")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                         "--master-addr", "127.0.0.1", "--master-port", str(29700 + world),
-                        os.path.join(ROOT, "tools", "dp_check.py")], capture_output=True, text=True, timeout=900)
+                        os.path.join(ROOT, "tools", "dp_check.py")], capture_output=True, text=True, timeout=900, env=env)
     assert r.returncode == 0 and "DP_CHECK_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

@@ -37,7 +37,8 @@ def main():
         torch.manual_seed(0)
         oracle = Transformer(**CFG, N_BLOCKS=L).to(ctx.device)
     eng = model.engine
-    eng.dp = DataParallel(eng, ctx, mode=os.environ.get("DP_MODE", "ddp"))
+    eng.dp = DataParallel(eng, ctx, mode=os.environ.get("DP_MODE", "ddp"),
+                          vocab_parallel=os.environ.get("DP_VP", "0") == "1")
     losses = []
     for step in range(STEPS):
         x, y = batches(r, step)
@@ -60,6 +61,9 @@ def main():
     dist.all_gather_object(flags, bool(same))
     # (3) gather full state
     eng.dp.gather_full_state()
+    if eng.dp.vp is not None:
+        ref = eng.wb.clone(); dist.broadcast(ref, src=0); same2 = torch.equal(eng.wb, ref)
+        flags2 = [None] * W; dist.all_gather_object(flags2, bool(same2)); flags = flags2
     ok = all(flags)
     if r == 0:
         o = oracle.engine
