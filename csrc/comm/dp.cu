@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
                                                               long long start, long long n, float* __restrict__ m,
                                                               float* __restrict__ v, const float* __restrict__ hyper,
                                                               DpSlots slots, unsigned int* cta_counter, int* err, int zero_mode) {
+    pdl_sync();
     const int epoch = *epoch_dev;   // device-resident step counter: the same CUDA graph serves every step
     // ---- 1. handshake: every rank has finished writing this bucket's gradients
     if (threadIdx.x == 0) {
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
 }
 
 __global__ void dp_wait_done_kernel(const int* sig, int W, int nb, const int* epoch_dev, int* err) {
+    pdl_sync();
     const int epoch = *epoch_dev;
     const int i = threadIdx.x;
     if (i < W * nb) wait_flag(sig + W * nb + i, epoch, err);
@@ -190,8 +192,8 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
     S.n = n_slots;
     for (int k = 0; k < n_slots; ++k) { S.end[k] = h_slot_end[k]; S.fp32[k] = h_slot_fp32[k]; }
 #define DP_LAUNCH(W_)                                                                                            \
-    dp_reduce_adamw_kernel<W_><<<ctas, 512, 0, st>>>(P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
-                                                     (unsigned int*)cta_counter, err, zero_mode)
+    B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
+                                                     (unsigned int*)cta_counter, err, zero_mode))
     switch (world) {
         case 1: DP_LAUNCH(1); break;
         case 2: DP_LAUNCH(2); break;
@@ -206,6 +208,6 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
 extern "C" int b200_dp_wait_done(const int* sig, int world, int num_buckets, const int* epoch_dev, int* err,
                                  cudaStream_t st) {
     B200_REQUIRE(world * num_buckets <= 1024, "dp_wait_done: too many (rank, bucket) pairs");
-    dp_wait_done_kernel<<<1, 1024, 0, st>>>(sig, world, num_buckets, epoch_dev, err);
+    B200_CHECK_CUDA(b200_launch(dp_wait_done_kernel, dim3(1), dim3(1024), 0, st, sig, world, num_buckets, epoch_dev, err));
     B200_RETURN_LAUNCH_STATUS("dp_wait_done");
 }

@@ -51,6 +51,7 @@ __device__ __forceinline__ void vp_handshake(const VpPtrs& sig, int W, int rank,
 }
 
 __global__ void __launch_bounds__(256) vp_barrier_kernel(VpPtrs sig, int W, int rank, int slot, const int* epoch_dev, int* err) {
+    pdl_sync();
     vp_handshake(sig, W, rank, slot, *epoch_dev, err);
 }
 
@@ -58,6 +59,7 @@ __global__ void __launch_bounds__(256) vp_barrier_kernel(VpPtrs sig, int W, int 
 __global__ void __launch_bounds__(256) vp_gather_rows_kernel(VpPtrs hf, VpPtrs tgt, bf16* __restrict__ dst_all,
                                                             long long* __restrict__ tgt_all, int M, int d, int W, int rank,
                                                             long long tgt_shift, VpPtrs sig, int slot, const int* epoch_dev, int* err) {
+    pdl_sync();
     vp_handshake(sig, W, rank, slot, *epoch_dev, err);
     const long long vec_per_rank = (long long)M * d / 8;
     const long long total = vec_per_rank * W;
@@ -79,6 +81,7 @@ __global__ void __launch_bounds__(128) vp_ce_finalize_kernel(VpPtrs stats, VpPtr
                                                             float* __restrict__ loss_rows, int M, int W, int rank, int V, int Vs,
                                                             int nt_local, long long ldl, float sum_scale, VpPtrs sig, int slot,
                                                             const int* epoch_dev, int* err) {
+    pdl_sync();
     vp_handshake(sig, W, rank, slot, *epoch_dev, err);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const long long Mw = (long long)M * W;
@@ -115,6 +118,7 @@ __global__ void __launch_bounds__(128) vp_ce_finalize_kernel(VpPtrs stats, VpPtr
 // out[i, :] = scale * sum_src partial[src][rank*M + i, :]
 __global__ void __launch_bounds__(256) vp_reduce_rows_kernel(VpPtrs partial, bf16* __restrict__ out, int M, int d, int W, int rank,
                                                             float scale, VpPtrs sig, int slot, const int* epoch_dev, int* err) {
+    pdl_sync();
     vp_handshake(sig, W, rank, slot, *epoch_dev, err);
     const long long nvec = (long long)M * d / 8;
     const long long base = (long long)rank * M * d / 8;
@@ -158,7 +162,7 @@ inline VpPtrs mk(void* const* h, int W) {
 extern "C" int b200_vp_barrier(void* const* h_sig, int world, int rank, int slot, const int* epoch_dev, int* err,
                                cudaStream_t st) {
     B200_REQUIRE(world <= VP_MAX_WORLD, "vp: world too large");
-    vp_barrier_kernel<<<1, 32, 0, st>>>(mk(h_sig, world), world, rank, slot, epoch_dev, err);
+    B200_CHECK_CUDA(b200_launch(vp_barrier_kernel, dim3(1), dim3(32), 0, st, mk(h_sig, world), world, rank, slot, epoch_dev, err));
     B200_RETURN_LAUNCH_STATUS("vp_barrier");
 }
 
@@ -166,8 +170,8 @@ extern "C" int b200_vp_gather_rows(void* const* h_hf, void* const* h_tgt, void* 
                                    int world, int rank, long long tgt_shift, void* const* h_sig, int slot, const int* epoch_dev,
                                    int* err, cudaStream_t st) {
     B200_REQUIRE(world <= VP_MAX_WORLD && ((long long)M * d) % 8 == 0, "vp_gather_rows: bad shape");
-    vp_gather_rows_kernel<<<b200_num_sms() * 2, 256, 0, st>>>(mk(h_hf, world), mk(h_tgt, world), (bf16*)dst_all, tgt_all, M, d,
-                                                              world, rank, tgt_shift, mk(h_sig, world), slot, epoch_dev, err);
+    B200_CHECK_CUDA(b200_launch(vp_gather_rows_kernel, dim3(b200_num_sms() * 2), dim3(256), 0, st, mk(h_hf, world), mk(h_tgt, world), (bf16*)dst_all, tgt_all, M, d,
+                                                              world, rank, tgt_shift, mk(h_sig, world), slot, epoch_dev, err));
     B200_RETURN_LAUNCH_STATUS("vp_gather_rows");
 }
 
@@ -176,16 +180,16 @@ extern "C" int b200_vp_ce_finalize(void* const* h_stats, void* const* h_logits, 
                                    long long ldl, float sum_scale, void* const* h_sig, int slot, const int* epoch_dev, int* err,
                                    cudaStream_t st) {
     B200_REQUIRE(world <= VP_MAX_WORLD, "vp: world too large");
-    vp_ce_finalize_kernel<<<(M + 127) / 128, 128, 0, st>>>(mk(h_stats, world), mk(h_logits, world), mk(h_lse_all, world), targets,
+    B200_CHECK_CUDA(b200_launch(vp_ce_finalize_kernel, dim3((M + 127) / 128), dim3(128), 0, st, mk(h_stats, world), mk(h_logits, world), mk(h_lse_all, world), targets,
                                                            loss_sum, loss_rows, M, world, rank, V, Vs, nt_local, ldl, sum_scale,
-                                                           mk(h_sig, world), slot, epoch_dev, err);
+                                                           mk(h_sig, world), slot, epoch_dev, err));
     B200_RETURN_LAUNCH_STATUS("vp_ce_finalize");
 }
 
 extern "C" int b200_vp_reduce_rows(void* const* h_partial, void* out, int M, int d, int world, int rank, float scale,
                                    void* const* h_sig, int slot, const int* epoch_dev, int* err, cudaStream_t st) {
     B200_REQUIRE(world <= VP_MAX_WORLD && ((long long)M * d) % 8 == 0, "vp_reduce_rows: bad shape");
-    vp_reduce_rows_kernel<<<b200_num_sms() * 2, 256, 0, st>>>(mk(h_partial, world), (bf16*)out, M, d, world, rank, scale,
-                                                              mk(h_sig, world), slot, epoch_dev, err);
+    B200_CHECK_CUDA(b200_launch(vp_reduce_rows_kernel, dim3(b200_num_sms() * 2), dim3(256), 0, st, mk(h_partial, world), (bf16*)out, M, d, world, rank, scale,
+                                                              mk(h_sig, world), slot, epoch_dev, err));
     B200_RETURN_LAUNCH_STATUS("vp_reduce_rows");
 }

@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(256) adamw_kernel(float* __restrict__ p, const
                                                     float* __restrict__ m, float* __restrict__ v,
                                                     bf16* __restrict__ pb, const float* __restrict__ hyper,
                                                     long long n) {
+    pdl_sync();
     const float decay = hyper[0], b2 = hyper[1], w1 = hyper[2], w2 = hyper[3], step_size = hyper[4],
                 bc2s = hyper[5], eps = hyper[6], gs = hyper[7];
     const long long n4 = n >> 2;
@@ -66,6 +67,6 @@ extern "C" int b200_adamw(float* p, const float* g, float* m, float* v, void* p_
     const long long cap = (long long)b200_num_sms() * 8;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    adamw_kernel<<<(int)blocks, 256, 0, st>>>(p, g, m, v, (bf16*)p_bf16, hyper, n);
+    B200_CHECK_CUDA(b200_launch(adamw_kernel, dim3((int)blocks), dim3(256), 0, st, p, g, m, v, (bf16*)p_bf16, hyper, n));
     B200_RETURN_LAUNCH_STATUS("adamw");
 }

@@ -92,6 +92,7 @@ template <int HD>
 __global__ void __launch_bounds__(FWD_THREADS) attn_fwd_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out,
                                                               float* __restrict__ lse_out, int T, int H,
                                                               float scale_log2) {
+    pdl_sync();
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sQ = smem_u32(smem);
     const uint32_t sK = sQ + FWD_BM * HD * 2;            // 2 stages
@@ -255,6 +256,7 @@ __global__ void __launch_bounds__(FWD_THREADS) attn_fwd_kernel(const bf16* __res
 template <int HD>
 __global__ void __launch_bounds__(256) attn_bwd_delta_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout,
                                                             float* __restrict__ delta, int B, int T, int H) {
+    pdl_sync();
     // one warp per (row m, head h); lane handles HD/32 elements
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int total = B * T * H;
@@ -287,6 +289,7 @@ __global__ void __launch_bounds__(BWD_THREADS) attn_bwd_kernel(const bf16* __res
                                                               const float* __restrict__ delta,
                                                               float* __restrict__ dq_acc, bf16* __restrict__ dqkv, int T,
                                                               int H, float scale, float scale_log2) {
+    pdl_sync();
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int TILE = 64 * HD * 2;
     const uint32_t sK = smem_u32(smem);
@@ -477,6 +480,7 @@ __global__ void __launch_bounds__(BWD_THREADS) attn_bwd_kernel(const bf16* __res
 // dq_acc fp32 [M, H*hs] -> q third of dqkv (bf16), and re-zero dq_acc for the next call
 __global__ void __launch_bounds__(256) attn_bwd_dq_store_kernel(float* __restrict__ dq_acc, bf16* __restrict__ dqkv,
                                                                long long M, int HHD) {
+    pdl_sync();
     const long long n4 = M * HHD / 4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         float4 v = reinterpret_cast<float4*>(dq_acc)[i];
@@ -497,7 +501,7 @@ int attn_fwd_launch(const bf16* qkv, bf16* out, float* lse, int B, int T, int H,
         cfg = true;
     }
     dim3 grid((T + FWD_BM - 1) / FWD_BM, H, B);
-    attn_fwd_kernel<HD><<<grid, FWD_THREADS, SMEM, st>>>(qkv, out, lse, T, H, scale * 1.4426950408889634f);
+    B200_CHECK_CUDA(b200_launch(attn_fwd_kernel<HD>, dim3(grid), dim3(FWD_THREADS), SMEM, st, qkv, out, lse, T, H, scale * 1.4426950408889634f));
     return 0;
 }
 
@@ -512,12 +516,12 @@ int attn_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, const fl
         cfg = true;
     }
     const int total_warps = B * T * H;
-    attn_bwd_delta_kernel<HD><<<(total_warps + 7) / 8, 256, 0, st>>>(out, dout, delta, B, T, H);
+    B200_CHECK_CUDA(b200_launch(attn_bwd_delta_kernel<HD>, dim3((total_warps + 7) / 8), dim3(256), 0, st, out, dout, delta, B, T, H));
     dim3 grid((T + BWD_BN - 1) / BWD_BN, H, B);
-    attn_bwd_kernel<HD><<<grid, BWD_THREADS, SMEM, st>>>(qkv, dout, lse, delta, dq_acc, dqkv, T, H, scale,
-                                                         scale * 1.4426950408889634f);
+    B200_CHECK_CUDA(b200_launch(attn_bwd_kernel<HD>, dim3(grid), dim3(BWD_THREADS), SMEM, st, qkv, dout, lse, delta, dq_acc, dqkv, T, H, scale,
+                                                         scale * 1.4426950408889634f));
     const long long M = (long long)B * T;
-    attn_bwd_dq_store_kernel<<<b200_num_sms() * 8, 256, 0, st>>>(dq_acc, dqkv, M, H * HD);
+    B200_CHECK_CUDA(b200_launch(attn_bwd_dq_store_kernel, dim3(b200_num_sms() * 8), dim3(256), 0, st, dq_acc, dqkv, M, H * HD));
     return 0;
 }
 

@@ -93,6 +93,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
+    pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base));
 
     if (warp == 0) {
@@ -298,7 +299,7 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, floa
         cfg = true;
     }
     dim3 grid((T + BM - 1) / BM, H, B);
-    kern<<<grid, NTHREADS, C::SMEM, st>>>(tq, to, lse, T, H, scale * 1.4426950408889634f);
+    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NTHREADS), C::SMEM, st, tq, to, lse, T, H, scale * 1.4426950408889634f));
     return 0;
 }
 
@@ -341,6 +342,7 @@ template <int HD, bool DKV> struct BCfg {
 template <int HD>
 __global__ void __launch_bounds__(256) attn_bwd_delta_tc_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout,
                                                                float* __restrict__ delta, int B, int T, int H) {
+    pdl_sync();
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (gw >= B * T * H) return;
     const int h = gw % H, m = gw / H;
@@ -416,6 +418,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
+    pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base));
 
     if (warp == 0) {
@@ -631,8 +634,8 @@ int launch_bwd_pass(const CUtensorMap& t128, const CUtensorMap& t64, const CUten
         cfg = true;
     }
     dim3 grid((T + 127) / 128, H, B);
-    kern<<<grid, NTHREADS, C::SMEM, st>>>(t128, t64, d128, d64, lse, delta, (bf16*)dqkv, T, H, scale,
-                                          scale * 1.4426950408889634f);
+    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NTHREADS), C::SMEM, st, t128, t64, d128, d64, lse, delta, (bf16*)dqkv, T, H, scale,
+                                          scale * 1.4426950408889634f));
     return 0;
 }
 
@@ -646,7 +649,7 @@ int launch_bwd(const void* qkv, const void* out, const void* dout, const float* 
     if (tma::make_3d(&d128, dout, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 128, 2)) return -1;
     if (tma::make_3d(&d64, dout, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 64, 2)) return -1;
     const int total_warps = B * T * H;
-    attn_bwd_delta_tc_kernel<HD><<<(total_warps + 7) / 8, 256, 0, st>>>((const bf16*)out, (const bf16*)dout, delta, B, T, H);
+    B200_CHECK_CUDA(b200_launch(attn_bwd_delta_tc_kernel<HD>, dim3((total_warps + 7) / 8), dim3(256), 0, st, (const bf16*)out, (const bf16*)dout, delta, B, T, H));
     if (launch_bwd_pass<HD, true>(t128, t64, d128, d64, lse, delta, dqkv, B, T, H, scale, st)) return -1;
     if (launch_bwd_pass<HD, false>(t128, t64, d128, d64, lse, delta, dqkv, B, T, H, scale, st)) return -1;
     return 0;

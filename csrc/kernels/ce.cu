@@ -13,6 +13,7 @@ __global__ void __launch_bounds__(256) ce_finalize_kernel(const float2* __restri
                                                           const long long* __restrict__ targets,
                                                           float* __restrict__ lse, float* __restrict__ loss_rows,
                                                           float* __restrict__ loss_sum, int M, int V, float sum_scale) {
+    pdl_sync();
     const int m = blockIdx.x * blockDim.x + threadIdx.x;
     float loss = 0.f;
     if (m < M) {
@@ -46,8 +47,8 @@ __global__ void __launch_bounds__(256) ce_finalize_kernel(const float2* __restri
 extern "C" int b200_ce_finalize(const void* stats, int n_tiles, const void* logits, long long ld,
                                 const long long* targets, float* lse, float* loss_rows, float* loss_sum, int M, int V,
                                 float sum_scale, cudaStream_t st) {
-    ce_finalize_kernel<<<(M + 255) / 256, 256, 0, st>>>((const float2*)stats, n_tiles, (const bf16*)logits, ld, targets,
-                                                        lse, loss_rows, loss_sum, M, V, sum_scale);
+    B200_CHECK_CUDA(b200_launch(ce_finalize_kernel, dim3((M + 255) / 256), dim3(256), 0, st, (const float2*)stats, n_tiles, (const bf16*)logits, ld, targets,
+                                                        lse, loss_rows, loss_sum, M, V, sum_scale));
     B200_RETURN_LAUNCH_STATUS("ce_finalize");
 }
 
@@ -58,6 +59,7 @@ __global__ void __launch_bounds__(256) ce_grad_kernel(bf16* __restrict__ logits,
                                                       const float* __restrict__ lse,
                                                       const long long* __restrict__ targets,
                                                       float* __restrict__ dbias, int M, int V, float scale) {
+    pdl_sync();
     const int col0 = (blockIdx.x * 256 + threadIdx.x) * 8;
     const int r0 = blockIdx.y * CE_ROWS, r1 = min(M, r0 + CE_ROWS);
     __shared__ float s_lse[CE_ROWS];
@@ -121,6 +123,6 @@ extern "C" int b200_ce_grad(void* logits, long long ld, const float* lse, const 
     B200_REQUIRE(ld % 8 == 0 && (uintptr_t)logits % 16 == 0, "ce_grad: ld must be a multiple of 8, logits 16B aligned");
     if (dbias != nullptr && !accumulate) B200_CHECK_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * (size_t)V, st));
     dim3 grid((V + 2047) / 2048, (M + CE_ROWS - 1) / CE_ROWS);
-    ce_grad_kernel<<<grid, 256, 0, st>>>((bf16*)logits, ld, lse, targets, dbias, M, V, scale);
+    B200_CHECK_CUDA(b200_launch(ce_grad_kernel, dim3(grid), dim3(256), 0, st, (bf16*)logits, ld, lse, targets, dbias, M, V, scale));
     B200_RETURN_LAUNCH_STATUS("ce_grad");
 }

@@ -10,6 +10,7 @@ __global__ void __launch_bounds__(256) embed_fwd_kernel(const long long* __restr
                                                         const float* __restrict__ wpe,
                                                         float* __restrict__ x, int M, int T, int d, int V,
                                                         int pos0, const int* __restrict__ pos_dev) {
+    pdl_sync();
     if (pos_dev != nullptr) pos0 = *pos_dev;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -32,7 +33,7 @@ extern "C" int b200_embed_fwd(const long long* idx, const float* wte, const floa
     B200_REQUIRE(d % 4 == 0, "embed_fwd: d must be a multiple of 4");
     int M = B * T;
     int blocks = min((M + 7) / 8, b200_num_sms() * 8);
-    embed_fwd_kernel<<<max(blocks, 1), 256, 0, st>>>(idx, wte, wpe, x, M, T, d, V, pos0, pos_dev);
+    B200_CHECK_CUDA(b200_launch(embed_fwd_kernel, dim3(max(blocks, 1)), dim3(256), 0, st, idx, wte, wpe, x, M, T, d, V, pos0, pos_dev));
     B200_RETURN_LAUNCH_STATUS("embed_fwd");
 }
 
@@ -42,6 +43,7 @@ extern "C" int b200_embed_fwd(const long long* idx, const float* wte, const floa
 __global__ void __launch_bounds__(256) embed_bwd_tok_kernel(const long long* __restrict__ idx,
                                                             const float* __restrict__ dx,
                                                             float* __restrict__ dwte, int M, int d, int V) {
+    pdl_sync();
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
     for (int m = warp; m < M; m += nwarps) {
@@ -60,6 +62,7 @@ __global__ void __launch_bounds__(256) embed_bwd_tok_kernel(const long long* __r
 
 __global__ void __launch_bounds__(256) embed_bwd_pos_kernel(const float* __restrict__ dx, float* __restrict__ dwpe,
                                                             int B, int T, int d, int accumulate) {
+    pdl_sync();
     const int total4 = T * d / 4;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
         float4 acc = accumulate ? reinterpret_cast<float4*>(dwpe)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -76,9 +79,9 @@ extern "C" int b200_embed_bwd(const long long* idx, const float* dx, float* dwte
     B200_REQUIRE(d % 4 == 0, "embed_bwd: d must be a multiple of 4");
     int M = B * T;
     int blocks = min((M + 7) / 8, b200_num_sms() * 8);
-    embed_bwd_tok_kernel<<<max(blocks, 1), 256, 0, st>>>(idx, dx, dwte, M, d, V);
+    B200_CHECK_CUDA(b200_launch(embed_bwd_tok_kernel, dim3(max(blocks, 1)), dim3(256), 0, st, idx, dx, dwte, M, d, V));
     int total4 = T * d / 4;
     int blocks2 = min((total4 + 255) / 256, b200_num_sms() * 8);
-    embed_bwd_pos_kernel<<<max(blocks2, 1), 256, 0, st>>>(dx, dwpe, B, T, d, accumulate);
+    B200_CHECK_CUDA(b200_launch(embed_bwd_pos_kernel, dim3(max(blocks2, 1)), dim3(256), 0, st, dx, dwpe, B, T, d, accumulate));
     B200_RETURN_LAUNCH_STATUS("embed_bwd");
 }

@@ -85,6 +85,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
+    pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
     const int ntiles = p.num_m * p.num_n;
@@ -200,7 +201,7 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, 
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
         configured = true;
     }
-    kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, st>>>(tA, tB, tC, p);
+    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NUM_THREADS), Cfg<BN>::SMEM_BYTES, st, tA, tB, tC, p));
     return 0;
 }
 

@@ -91,6 +91,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
+    pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
     const int ntiles = p.num_m * p.num_n;        // num_m counts 256-row tiles here
@@ -259,7 +260,7 @@ int launch2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
     }
     AgParams none;
     memset(&none, 0, sizeof(none));
-    kern<<<grid, AG ? NUM_THREADS + 128 : NUM_THREADS, Cfg2<BN>::SMEM_BYTES, st>>>(tA, tB, tC, p, ag ? *ag : none);
+    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(AG ? NUM_THREADS + 128 : NUM_THREADS), Cfg2<BN>::SMEM_BYTES, st, tA, tB, tC, p, ag ? *ag : none));
     return 0;
 }
 

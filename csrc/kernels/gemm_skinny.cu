@@ -1,0 +1,247 @@
+// Weight-streaming GEMM for decode-sized batches:  out[M, N] = act(x[M, K] @ W[N, K]^T + bias),  M <= 128.
+//
+// At M = 32 the problem is a stream of the weight matrix through the SM (2 bytes per 64 MACs): the 128 x 256 tile
+// kernel wastes 3/4 of every MMA on padding and, worse, has too few CTAs and too few bytes in flight to pull
+// HBM bandwidth.  Here the operands are SWAPPED: the weight tile is the M = 128 operand of tcgen05.mma and the
+// batch is the N operand (N = 32/64/128), so a CTA's smem ring holds 10 x 16 KiB of weights in flight, the
+// accumulator is a 128 x M tile in TMEM (<= 128 columns), and K is split across CTAs so every GEMM of a decode
+// step has ~one CTA per SM.  The CTAs that share a weight-row tile form a THREAD-BLOCK CLUSTER (2, 4 or 8 CTAs
+// along K): each leaves its fp32 partial tile in its own shared memory, and after a cluster barrier every CTA
+// reduces a slice of the batch rows by reading its peers' tiles through distributed shared memory - no global
+// scratch, no atomics, no second kernel.
+// Replaces the per-token full-context fp32 forward of the reference's generate (src/models/transformer.py:107-113).
+#include <cuda.h>
+
+#include "b200llm.h"
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tma.cuh"
+
+namespace {
+
+constexpr int BK = 64;
+constexpr int A_BYTES = 128 * BK * 2;
+constexpr int NUM_THREADS = 192;
+
+template <int NB> struct SCfg {
+    static constexpr int B_BYTES = NB * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = NB == 32 ? 10 : (NB == 64 ? 8 : 6);
+    static constexpr int TMEM_COLS = NB < 32 ? 32 : NB;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 + 1024;
+};
+
+struct SParams {
+    int M, N, K, num_kb, splits, kb_per_split;
+    const float* bias;
+    int relu;
+    bf16* out;
+    long long ldc;
+};
+
+template <int NB>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const SParams p) {
+    using C = SCfg<NB>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
+    const uint32_t done_bar = bar_base + 8u * (2 * C::STAGES);
+    const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 1);
+    uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tile = blockIdx.x, split = blockIdx.y;
+    const int n0 = n_tile * 128;
+    const int kb0 = split * p.kb_per_split;
+    const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmW);
+        ptx::prefetch_tmap(&tmX);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < C::STAGES; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+        ptx::mbar_init(done_bar, 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) {
+        ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                ptx::mbar_wait(empty_bar(stage), phase ^ 1);
+                ptx::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+                const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+                ptx::tma_load_2d(sa, &tmW, full_bar(stage), kb * BK, n0);            // 128 weight rows
+                ptx::tma_load_2d(sa + A_BYTES, &tmX, full_bar(stage), kb * BK, 0);   // the whole (padded) batch
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, NB, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                ptx::mbar_wait(full_bar(stage), phase);
+                ptx::tc_fence_after();
+                const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+                const uint64_t adesc = ptx::umma_desc(sa, 16, 1024);
+                const uint64_t bdesc = ptx::umma_desc(sa + A_BYTES, 16, 1024);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k)
+                    ptx::mma_bf16_ss(tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                ptx::mma_commit(empty_bar(stage));
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+            }
+            ptx::mma_commit(done_bar);
+        }
+    } else {
+        // epilogue: thread = weight row n (TMEM lane), NB accumulator columns = batch rows
+        const int q = warp & 3;
+        const int n = n0 + q * 32 + lane;
+        ptx::mbar_wait(done_bar, 0);
+        ptx::tc_fence_after();
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+        const float b = (p.bias != nullptr && n < p.N) ? __ldg(p.bias + n) : 0.f;
+        if (p.splits == 1) {
+#pragma unroll 1
+            for (int c = 0; c < NB / 32; ++c) {
+                uint32_t r[32];
+                ptx::tmem_ld_32x32(taddr + c * 32, r);
+                ptx::tmem_ld_wait();
+                if (n < p.N) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int m = c * 32 + j;
+                        if (m < p.M) {
+                            float v = __uint_as_float(r[j]) + b;
+                            if (p.relu) v = fmaxf(v, 0.f);
+                            p.out[(size_t)m * p.ldc + n] = __float2bfloat16_rn(v);
+                        }
+                    }
+                }
+            }
+        } else {
+            // partial tile -> own smem (stage 0 is free: every MMA has retired), layout [m][128] fp32
+            float* part = reinterpret_cast<float*>(smem_gen);
+            const int nl = q * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < NB / 32; ++c) {
+                uint32_t r[32];
+                ptx::tmem_ld_32x32(taddr + c * 32, r);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) part[(c * 32 + j) * 128 + nl] = (kb1 > kb0) ? __uint_as_float(r[j]) : 0.f;  // empty K slice
+            }
+        }
+    }
+    if (p.splits > 1) {
+        // all CTAs of the cluster have published their partial tiles
+        ptx::cluster_sync_all();
+        if (warp >= 2) {
+            const int q = warp & 3;
+            const int nl = q * 32 + lane;
+            const int n = n0 + nl;
+            const float b = (p.bias != nullptr && n < p.N) ? __ldg(p.bias + n) : 0.f;
+            const int rows = (p.M + p.splits - 1) / p.splits;          // batch rows reduced by this CTA
+            const int m_lo = split * rows, m_hi = min(p.M, m_lo + rows);
+            const uint32_t local = smem_base;                          // same offset in every CTA of the cluster
+            for (int m = m_lo; m < m_hi; ++m) {
+                float v = b;
+                for (int s2 = 0; s2 < p.splits; ++s2) {
+                    float t;
+                    const uint32_t ra = ptx::mapa(local + (uint32_t)(m * 128 + nl) * 4u, (uint32_t)s2);
+                    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(t) : "r"(ra) : "memory");
+                    v += t;
+                }
+                if (p.relu) v = fmaxf(v, 0.f);
+                if (n < p.N) p.out[(size_t)m * p.ldc + n] = __float2bfloat16_rn(v);
+            }
+        }
+        ptx::cluster_sync_all();                                       // nobody leaves while its tile may still be read
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem, C::TMEM_COLS);
+    }
+}
+
+template <int NB>
+int launch_skinny(const CUtensorMap& tW, const CUtensorMap& tX, const SParams& p, dim3 grid, cudaStream_t st) {
+    auto kern = gemm_skinny_kernel<NB>;
+    static bool configured = false;
+    if (!configured) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SCfg<NB>::SMEM_BYTES));
+        configured = true;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = SCfg<NB>::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;      // the K splits of one weight tile share a cluster
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = grid.y;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    const char* e = getenv("B200_PDL");
+    cfg.attrs = attr;
+    cfg.numAttrs = (e != nullptr && e[0] == '1') ? 2 : 1;      // PDL is opt-in (see common.cuh)
+    B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tW, tX, p));
+    return 0;
+}
+
+}  // namespace
+
+// K split (= cluster size) chosen for (M, N, K): a power of two <= 8 giving about one CTA per SM
+extern "C" int b200_gemm_skinny_splits(int M, int N, int K) {
+    const int sms = b200_num_sms();
+    const int n_tiles = (N + 127) / 128, num_kb = (K + BK - 1) / BK;
+    int splits = 1;
+    while (splits < 8 && n_tiles * splits * 2 <= sms + sms / 4 && num_kb / (splits * 2) >= 4) splits *= 2;
+    (void)M;
+    return splits;
+}
+
+extern "C" int b200_gemm_skinny(const void* x, const void* W, void* out, int M, int N, int K, long long ldx, long long ldw,
+                                long long ldc, const float* bias, int relu, int split_k, cudaStream_t st) {
+    B200_REQUIRE(M >= 1 && M <= 128, "gemm_skinny: M must be in [1, 128] (got %d)", M);
+    B200_REQUIRE(ldx % 8 == 0 && ldw % 8 == 0 && K % 8 == 0, "gemm_skinny: K / leading dimensions must be multiples of 8");
+    const int NB = M <= 32 ? 32 : (M <= 64 ? 64 : 128);
+    SParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = N; p.K = K;
+    p.num_kb = (K + BK - 1) / BK;
+    p.splits = split_k > 0 ? split_k : b200_gemm_skinny_splits(M, N, K);
+    B200_REQUIRE(p.splits == 1 || p.splits == 2 || p.splits == 4 || p.splits == 8, "gemm_skinny: split_k must be 1, 2, 4 or 8");
+    while (p.splits > 1 && p.num_kb < p.splits) p.splits /= 2;
+    p.kb_per_split = (p.num_kb + p.splits - 1) / p.splits;
+    p.bias = bias; p.relu = relu; p.out = (bf16*)out; p.ldc = ldc;
+    CUtensorMap tW, tX;
+    if (tma::make_2d(&tW, W, N, K, ldw * 2, 64, 128, 2)) return -1;
+    if (tma::make_2d(&tX, x, M, K, ldx * 2, 64, NB, 2)) return -1;
+    dim3 grid((N + 127) / 128, p.splits);
+    int rc = NB == 32 ? launch_skinny<32>(tW, tX, p, grid, st)
+           : NB == 64 ? launch_skinny<64>(tW, tX, p, grid, st) : launch_skinny<128>(tW, tX, p, grid, st);
+    if (rc) return rc;
+    B200_RETURN_LAUNCH_STATUS("gemm_skinny");
+}

@@ -13,6 +13,7 @@ namespace {
 __global__ void __launch_bounds__(256) kv_append_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ kc,
                                                         bf16* __restrict__ vc, int B, int t, int H, int hs, int Tmax,
                                                         int pos0, const int* __restrict__ pos_dev) {
+    pdl_sync();
     if (pos_dev != nullptr) pos0 = *pos_dev;
     const int cpr = hs / 8;  // 16-byte chunks per (row, head)
     const long long total = (long long)B * t * H * cpr;
@@ -37,6 +38,7 @@ __global__ void __launch_bounds__(DEC_WARPS * 32) attn_decode_kernel(const bf16*
                                                                      const bf16* __restrict__ vc, bf16* __restrict__ out,
                                                                      int H, int Tmax, int len, float scale,
                                                                      const int* __restrict__ pos_dev) {
+    pdl_sync();
     if (pos_dev != nullptr) len = *pos_dev + 1;
     constexpr int VPL = HD / 32;  // output columns per lane
     __shared__ float s_q[HD];
@@ -128,6 +130,7 @@ __global__ void __launch_bounds__(SAMP_THREADS) sample_kernel(const bf16* __rest
                                                               long long* __restrict__ next, int V, float inv_temp,
                                                               unsigned long long seed, unsigned long long step,
                                                               const int* __restrict__ pos_dev) {
+    pdl_sync();
     if (pos_dev != nullptr) step += (unsigned long long)*pos_dev;
     __shared__ float s_red[32];
     __shared__ int s_pick;
@@ -200,8 +203,8 @@ extern "C" int b200_kv_append(const void* qkv, void* kcache, void* vcache, int B
     long long nb = (total + 255) / 256;
     const long long cap = (long long)b200_num_sms() * 8;
     const int blocks = (int)(nb < cap ? nb : cap);
-    kv_append_kernel<<<max(blocks, 1), 256, 0, st>>>((const bf16*)qkv, (bf16*)kcache, (bf16*)vcache, B, t, H, hs, Tmax,
-                                                      pos0, pos_dev);
+    B200_CHECK_CUDA(b200_launch(kv_append_kernel, dim3(max(blocks, 1)), dim3(256), 0, st, (const bf16*)qkv, (bf16*)kcache, (bf16*)vcache, B, t, H, hs, Tmax,
+                                                      pos0, pos_dev));
     B200_RETURN_LAUNCH_STATUS("kv_append");
 }
 
@@ -211,11 +214,11 @@ extern "C" int b200_attn_decode(const void* qkv, const void* kcache, const void*
     B200_REQUIRE(len >= 1 && len <= Tmax, "attn_decode: bad len");
     dim3 grid(H, B);
     if (hs == 64)
-        attn_decode_kernel<64><<<grid, DEC_WARPS * 32, 0, st>>>((const bf16*)qkv, (const bf16*)kcache,
-                                                                (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev);
+        B200_CHECK_CUDA(b200_launch(attn_decode_kernel<64>, dim3(grid), dim3(DEC_WARPS * 32), 0, st, (const bf16*)qkv, (const bf16*)kcache,
+                                                                (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev));
     else
-        attn_decode_kernel<128><<<grid, DEC_WARPS * 32, 0, st>>>((const bf16*)qkv, (const bf16*)kcache,
-                                                                 (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev);
+        B200_CHECK_CUDA(b200_launch(attn_decode_kernel<128>, dim3(grid), dim3(DEC_WARPS * 32), 0, st, (const bf16*)qkv, (const bf16*)kcache,
+                                                                 (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev));
     B200_RETURN_LAUNCH_STATUS("attn_decode");
 }
 
@@ -223,31 +226,34 @@ extern "C" int b200_sample(const void* logits, long long ld, long long* next, in
                            unsigned long long seed, unsigned long long step, const int* pos_dev, cudaStream_t st) {
     B200_REQUIRE(top_k <= 0, "sample: top_k filtering is applied by the caller (mask logits), pass top_k=0");
     B200_REQUIRE(temperature > 0.f, "sample: temperature must be > 0");
-    sample_kernel<<<B, SAMP_THREADS, 0, st>>>((const bf16*)logits, ld, next, V, 1.f / temperature, seed, step, pos_dev);
+    B200_CHECK_CUDA(b200_launch(sample_kernel, dim3(B), dim3(SAMP_THREADS), 0, st, (const bf16*)logits, ld, next, V, 1.f / temperature, seed, step, pos_dev));
     B200_RETURN_LAUNCH_STATUS("sample");
 }
 
-__global__ void incr_kernel(int* p, int delta) { *p += delta; }
+__global__ void incr_kernel(int* p, int delta) {
+    pdl_sync(); *p += delta; }
 extern "C" int b200_incr_int(int* p, int delta, cudaStream_t st) {
-    incr_kernel<<<1, 1, 0, st>>>(p, delta);
+    B200_CHECK_CUDA(b200_launch(incr_kernel, dim3(1), dim3(1), 0, st, p, delta));
     B200_RETURN_LAUNCH_STATUS("incr_int");
 }
 
 // seq[b, col] = next[b]   (col = *pos_dev + 1 when pos_dev is given)
 __global__ void scatter_tokens_kernel(const long long* next, long long* seq, int B, long long ld, int col,
                                       const int* pos_dev) {
+    pdl_sync();
     if (pos_dev != nullptr) col = *pos_dev + 1;
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b < B) seq[(size_t)b * ld + col] = next[b];
 }
 extern "C" int b200_scatter_tokens(const long long* next, long long* seq, int B, long long ld, int col,
                                    const int* pos_dev, cudaStream_t st) {
-    scatter_tokens_kernel<<<(B + 127) / 128, 128, 0, st>>>(next, seq, B, ld, col, pos_dev);
+    B200_CHECK_CUDA(b200_launch(scatter_tokens_kernel, dim3((B + 127) / 128), dim3(128), 0, st, next, seq, B, ld, col, pos_dev));
     B200_RETURN_LAUNCH_STATUS("scatter_tokens");
 }
 
 // out[b, :] = in[(b * T + T - 1), :]  - last-position rows for the last-token-only LM head
 __global__ void gather_last_rows_kernel(const uint4* in, uint4* out, int B, int T, int row_chunks) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < B * row_chunks) {
         const int b = i / row_chunks, c = i % row_chunks;
@@ -257,6 +263,6 @@ __global__ void gather_last_rows_kernel(const uint4* in, uint4* out, int B, int 
 extern "C" int b200_gather_last_rows(const void* in, void* out, int B, int T, int row_bytes, cudaStream_t st) {
     B200_REQUIRE(row_bytes % 16 == 0, "gather_last_rows: row_bytes must be a multiple of 16");
     const int rc = row_bytes / 16;
-    gather_last_rows_kernel<<<(B * rc + 255) / 256, 256, 0, st>>>((const uint4*)in, (uint4*)out, B, T, rc);
+    B200_CHECK_CUDA(b200_launch(gather_last_rows_kernel, dim3((B * rc + 255) / 256), dim3(256), 0, st, (const uint4*)in, (uint4*)out, B, T, rc));
     B200_RETURN_LAUNCH_STATUS("gather_last_rows");
 }

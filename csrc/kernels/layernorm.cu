@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const float* x, float* x_ou
                                                      const float* __restrict__ beta, bf16* __restrict__ out,
                                                      float* __restrict__ out_f32, float* __restrict__ mean_out,
                                                      float* __restrict__ rstd_out, int M, float eps) {
+    pdl_sync();
     constexpr int G = 8 / WPR;
     constexpr int D4 = 32 * WPR * VPL;  // float4 per row
     __shared__ float sred_all[8];
@@ -103,6 +104,7 @@ __global__ void __launch_bounds__(256, 2)
     ln_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean,
                   const float* __restrict__ rstd, const float* __restrict__ gamma, const float* dx_in,
                   float* dx_out, bf16* __restrict__ dx_bf16, float* __restrict__ partial, int M) {
+    pdl_sync();
     constexpr int G = 8 / WPR;
     constexpr int D4 = 32 * WPR * VPL;
     constexpr int NACC = COLSUM ? 3 : 2;
@@ -201,6 +203,7 @@ __global__ void __launch_bounds__(256, 2)
 __global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int nacc,
                                                               int d, float* __restrict__ o0, float* __restrict__ o1,
                                                               float* __restrict__ o2, int accumulate) {
+    pdl_sync();
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + tx;
     const int k = blockIdx.y;
@@ -266,8 +269,10 @@ extern "C" int b200_ln_fwd(const float* x, const void* branch, float* x_out, con
     if (M <= 0) return 0;
     const int G = 8 / cfg.wpr;
     const int grid = (M + G - 1) / G;
-    LN_DISPATCH_ALL((ln_fwd_kernel<VPL, WPR><<<grid, 256, 0, st>>>(x, x_out, (const bf16*)branch, gamma, beta,
-                                                                   (bf16*)out_bf16, out_f32, mean, rstd, M, eps)))
+    LN_DISPATCH_ALL({
+        B200_CHECK_CUDA(b200_launch(ln_fwd_kernel<VPL, WPR>, dim3(grid), dim3(256), 0, st, x, x_out, (const bf16*)branch,
+                                    gamma, beta, (bf16*)out_bf16, out_f32, mean, rstd, M, eps));
+    })
     B200_RETURN_LAUNCH_STATUS("ln_fwd");
 }
 
@@ -299,18 +304,18 @@ extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, co
             auto kern = ln_bwd_kernel<VPL, WPR, true>;
             static bool cfg_done = false;
             if (!cfg_done) { B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304)); cfg_done = true; }
-            kern<<<grid, 256, smem, st>>>((const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M);
+            B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(256), smem, st, (const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M));
         })
     } else {
         LN_DISPATCH_ALL({
             auto kern = ln_bwd_kernel<VPL, WPR, false>;
             static bool cfg_done = false;
             if (!cfg_done) { B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304)); cfg_done = true; }
-            kern<<<grid, 256, smem, st>>>((const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M);
+            B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(256), smem, st, (const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M));
         })
     }
-    ln_bwd_finalize_kernel<<<dim3((d + 31) / 32, nacc), 256, 0, st>>>(partial, grid, nacc, d, dgamma, dbeta, colsum,
-                                                                       accumulate);
+    B200_CHECK_CUDA(b200_launch(ln_bwd_finalize_kernel, dim3(dim3((d + 31) / 32, nacc)), dim3(256), 0, st, partial, grid, nacc, d, dgamma, dbeta, colsum,
+                                                                       accumulate));
     B200_RETURN_LAUNCH_STATUS("ln_bwd");
 }
 

@@ -24,6 +24,7 @@ extern "C" int b200_abi_version() { return B200_ABI_VERSION; }
 // fp32 -> bf16 cast (n % 4 == 0 on the vector path, scalar tail)
 // ------------------------------------------------------------------------------------------
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long long n) {
+    pdl_sync();
     long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 4;
     long long stride = (long long)gridDim.x * blockDim.x * 4;
     for (; i + 3 < n; i += stride) {
@@ -43,7 +44,7 @@ extern "C" int b200_cast_f32_bf16(const float* in, void* out, long long n, cudaS
     long long cap = (long long)b200_num_sms() * 16;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    cast_f32_bf16_kernel<<<(int)blocks, threads, 0, st>>>(in, (bf16*)out, n);
+    B200_CHECK_CUDA(b200_launch(cast_f32_bf16_kernel, dim3((int)blocks), dim3(threads), 0, st, in, (bf16*)out, n));
     B200_RETURN_LAUNCH_STATUS("cast_f32_bf16");
 }
 
@@ -54,6 +55,7 @@ extern "C" int b200_cast_f32_bf16(const float* in, void* out, long long n, cudaS
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const bf16* __restrict__ a, float* __restrict__ out,
                                                           int M, int N, int ld, int rows_per_cta) {
+    pdl_sync();
     // thread (ty, tx): tx in [0,8) covers 8 columns (one 16-byte load), ty in [0,32) strides rows
     const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
     const int col0 = blockIdx.x * 64 + tx * 8;
@@ -99,7 +101,7 @@ extern "C" int b200_colsum_bf16(const void* a, float* out, int M, int N, int ld,
     int rows = (M + gy - 1) / gy;
     rows = (rows + 31) / 32 * 32;
     gy = (M + rows - 1) / rows;
-    colsum_bf16_kernel<<<dim3(gx, gy), 256, 0, st>>>((const bf16*)a, out, M, N, ld, rows);
+    B200_CHECK_CUDA(b200_launch(colsum_bf16_kernel, dim3(dim3(gx, gy)), dim3(256), 0, st, (const bf16*)a, out, M, N, ld, rows));
     B200_RETURN_LAUNCH_STATUS("colsum_bf16");
 }
 
@@ -107,12 +109,13 @@ extern "C" int b200_colsum_bf16(const void* a, float* out, int M, int N, int ld,
 // L2 flush helper for benchmarks: overwrite a buffer larger than L2.
 // ------------------------------------------------------------------------------------------
 __global__ void fill_kernel(float4* p, long long n4, float v) {
+    pdl_sync();
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     long long stride = (long long)gridDim.x * blockDim.x;
     for (; i < n4; i += stride) p[i] = make_float4(v, v, v, v);
 }
 
 extern "C" int b200_l2_flush(void* buf, long long bytes, cudaStream_t st) {
-    fill_kernel<<<b200_num_sms() * 8, 256, 0, st>>>((float4*)buf, bytes / 16, 0.f);
+    B200_CHECK_CUDA(b200_launch(fill_kernel, dim3(b200_num_sms() * 8), dim3(256), 0, st, (float4*)buf, bytes / 16, 0.f));
     B200_RETURN_LAUNCH_STATUS("l2_flush");
 }

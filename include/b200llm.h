@@ -81,6 +81,13 @@ int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, l
  * raise flags[c] = *epoch_dev; tiles whose rows are already local run meanwhile, the others wait per chunk. */
 int b200_gemm_ag(const void* A, void* C, int M, int N, int K, long long lda, long long ldc, const float* bias, int relu, void* const* h_wb, int world, int rank, long long layer_start, long long layer_end, long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev, int gather, cudaStream_t st);
 
+/* Weight-streaming GEMM for decode-sized batches (M <= 128): out[M,N] = act(x[M,K] @ W[N,K]^T + bias), operands
+ * swapped so the weight tile is the 128-row MMA operand; K is split over the CTAs of a thread-block cluster
+ * (split_k = 0: chosen automatically, else 1/2/4/8) whose partial tiles are combined through distributed shared
+ * memory - no scratch, no atomics. */
+int b200_gemm_skinny_splits(int M, int N, int K);
+int b200_gemm_skinny(const void* x, const void* W, void* out, int M, int N, int K, long long ldx, long long ldw, long long ldc, const float* bias, int relu, int split_k, cudaStream_t st);
+
 /* ---- fused AdamW (ref: scripts/train_transformer.py:92,126 torch.optim.AdamW defaults) -------
  * hyper (device, 8 floats) = 1 - lr*weight_decay, beta2, 1 - beta1, 1 - beta2, lr / bias_correction1,
  * sqrt(bias_correction2), eps, grad_scale (derive them in double on the host: ops.adamw_hyper).

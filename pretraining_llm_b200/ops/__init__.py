@@ -91,6 +91,19 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     return out
 
 
+def gemm_skinny(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None, *, bias=None, relu: bool = False,
+                split_k: int = 0) -> torch.Tensor:
+    """out[M,N] = act(x[M,K] @ w[N,K]^T + bias) for M <= 128 (decode): the weight-streaming tcgen05 kernel
+    (K split across a thread-block cluster, partials reduced through distributed shared memory)."""
+    M, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty(M, N, device=x.device, dtype=BF16)
+    _chk(lib.load().b200_gemm_skinny(_p(x), _p(w), _p(out), M, N, K, x.stride(0), w.stride(0), out.stride(0), _p(bias),
+                                     int(relu), split_k, _st()), "gemm_skinny")
+    return out
+
+
 def gemm_pick_bn(M: int, N: int, K: int, out_f32: bool = False) -> int:
     return lib.load().b200_gemm_pick_bn(M, N, K, int(out_f32))
 

@@ -63,10 +63,17 @@ class Generator:
         return b
 
     # ------------------------------------------------------------------ pieces
-    def _head(self, hf: torch.Tensor, logits: torch.Tensor) -> None:
+    def _gemm(self, db, x, w, out, bias=None, relu=False) -> None:
+        """Decode-sized GEMM: weight-streaming kernel when the batch fits one MMA operand, tile kernel otherwise."""
+        if db is not None and x.shape[0] <= 128:
+            ops.gemm_skinny(x, w, out, bias=bias, relu=relu)
+        else:
+            ops.gemm(x, w, out=out, bias=bias, relu=relu)
+
+    def _head(self, hf: torch.Tensor, logits: torch.Tensor, db=None) -> None:
         eng = self.eng
         V = eng.layout.V
-        ops.gemm(hf, eng.W("lm_head.weight"), out=logits[:, :V], bias=eng.P("lm_head.bias"))
+        self._gemm(db, hf, eng.W("lm_head.weight"), logits[:, :V], bias=eng.P("lm_head.bias"))
 
     def _prefill(self, idx: torch.Tensor, db: Optional[_DecodeBuffers], logits: torch.Tensor) -> None:
         """Forward over the prompt; fills the KV cache (if db) and the last-position logits."""
@@ -79,7 +86,7 @@ class Generator:
         eng._blocks_forward(w, kv=(db.kc, db.vc) if db is not None else None, pos0=0)
         hf_last = db.hf if db is not None else torch.empty(B, eng.layout.d, device=eng.device, dtype=BF16)
         ops.gather_last_rows(w.hf, hf_last, B, T)
-        self._head(hf_last, logits)
+        self._head(hf_last, logits, db)
 
     def _decode_step(self, db: _DecodeBuffers, temperature: float, seed: int, sample: bool = True) -> None:
         """One token for every row: reads db.next_tok / db.pos, writes db.logits, db.next_tok, db.seq."""
@@ -95,17 +102,16 @@ class Generator:
             else:
                 ops.ln_fwd(db.rb, eng.P(pre + "ln1.weight"), eng.P(pre + "ln1.bias"), branch=db.mlp_out,
                            x_out=db.ra, out=db.h, want_stats=False)
-            ops.gemm(db.h, eng.W(pre + "attn.wqkv"), out=db.qkv)
+            self._gemm(db, db.h, eng.W(pre + "attn.wqkv"), db.qkv)
             ops.kv_append(db.qkv, db.kc[l], db.vc[l], B, 1, H, hs, ctx, pos_dev=db.pos)
             ops.attn_decode(db.qkv, db.kc[l], db.vc[l], db.att, B, H, hs, ctx, pos_dev=db.pos)
             ops.ln_fwd(db.ra, eng.P(pre + "ln2.weight"), eng.P(pre + "ln2.bias"), branch=db.att, x_out=db.rb,
                        out=db.h, want_stats=False)
-            ops.gemm(db.h, eng.W(pre + "mlp.hidden.weight"), out=db.act, bias=eng.P(pre + "mlp.hidden.bias"),
-                     relu=True)
-            ops.gemm(db.act, eng.W(pre + "mlp.proj.weight"), out=db.mlp_out, bias=eng.P(pre + "mlp.proj.bias"))
+            self._gemm(db, db.h, eng.W(pre + "mlp.hidden.weight"), db.act, bias=eng.P(pre + "mlp.hidden.bias"), relu=True)
+            self._gemm(db, db.act, eng.W(pre + "mlp.proj.weight"), db.mlp_out, bias=eng.P(pre + "mlp.proj.bias"))
         ops.ln_fwd(db.rb, eng.P("layer_norm.weight"), eng.P("layer_norm.bias"), branch=db.mlp_out, x_out=db.ra,
                    out=db.hf, want_stats=False)
-        self._head(db.hf, db.logits)
+        self._head(db.hf, db.logits, db)
         if sample:
             ops.sample(db.logits, db.next_tok, lay.V, temperature=temperature, seed=seed, step=1, pos_dev=db.pos)
             ops.scatter_tokens(db.next_tok, db.seq, pos_dev=db.pos)

@@ -68,6 +68,19 @@ def test_gemm_2cta(ops, bn, major):
     assert _rel(c, big_a.float() @ big_b.float().t()) < 6e-3
 
 
+@pytest.mark.parametrize("M", [1, 3, 32, 48, 128])
+def test_gemm_skinny(ops, M):
+    """Decode-sized weight-streaming GEMM: automatic and forced cluster split-K (DSMEM reduction)."""
+    torch.manual_seed(12 + M)
+    for (N, K) in ((6144, 2048), (2048, 8192), (1000, 328)):
+        x, w = _rand(M, K), _rand(N, K, scale=0.05)
+        bias = torch.randn(N, device="cuda")
+        ref = F.relu(x.float() @ w.float().t() + bias)
+        for sk in (0, 1, 2, 4, 8):
+            out = ops.gemm_skinny(x, w, bias=bias, relu=True, split_k=sk)
+            assert _rel(out, ref) < 6e-3, (N, K, sk, _rel(out, ref))
+
+
 def test_gemm_epilogues(ops):
     torch.manual_seed(1)
     M, N, K = 512, 1024, 256
