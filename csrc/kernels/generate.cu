@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(DEC_WARPS * 32) attn_decode_kernel(const bf16*
                                                                      const bf16* __restrict__ kc,
                                                                      const bf16* __restrict__ vc, bf16* __restrict__ out,
                                                                      int H, int Tmax, int len, float scale,
-                                                                     const int* __restrict__ pos_dev) {
+                                                                     const int* __restrict__ pos_dev, int append) {
     pdl_sync();
     if (pos_dev != nullptr) len = *pos_dev + 1;
     constexpr int VPL = HD / 32;  // output columns per lane
@@ -46,11 +46,18 @@ __global__ void __launch_bounds__(DEC_WARPS * 32) attn_decode_kernel(const bf16*
     __shared__ float s_acc[DEC_WARPS][HD];
     const int h = blockIdx.x, b = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x < HD)
-        s_q[threadIdx.x] = __bfloat162float(qkv[(size_t)b * 3 * H * HD + h * HD + threadIdx.x]) * scale;
-    __syncthreads();
     const bf16* kb = kc + ((size_t)b * H + h) * Tmax * HD;
     const bf16* vb = vc + ((size_t)b * H + h) * Tmax * HD;
+    if (threadIdx.x < HD) {
+        const size_t qoff = (size_t)b * 3 * H * HD + h * HD + threadIdx.x;
+        s_q[threadIdx.x] = __bfloat162float(qkv[qoff]) * scale;
+        if (append) {
+            // fused KV-cache append: this position's key / value rows go into the cache before they are attended to
+            const_cast<bf16*>(kb)[(size_t)(len - 1) * HD + threadIdx.x] = qkv[qoff + (size_t)H * HD];
+            const_cast<bf16*>(vb)[(size_t)(len - 1) * HD + threadIdx.x] = qkv[qoff + 2 * (size_t)H * HD];
+        }
+    }
+    __syncthreads();
 
     float m = -INFINITY, l = 0.f, acc[VPL];
 #pragma unroll
@@ -65,7 +72,7 @@ __global__ void __launch_bounds__(DEC_WARPS * 32) attn_decode_kernel(const bf16*
             float d = 0.f;
 #pragma unroll
             for (int c = 0; c < HD / 8; ++c) {
-                const uint4 u = ldg_stream_u4(kr + c);
+                const uint4 u = append ? kr[c] : __ldg(kr + c);   // L1-allocating: a lane walks its key row 16 B at a time
                 const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z),
                              f3 = unpack_bf16x2(u.w);
                 d += f0.x * s_q[c * 8] + f0.y * s_q[c * 8 + 1] + f1.x * s_q[c * 8 + 2] + f1.y * s_q[c * 8 + 3] +
@@ -208,17 +215,17 @@ extern "C" int b200_kv_append(const void* qkv, void* kcache, void* vcache, int B
     B200_RETURN_LAUNCH_STATUS("kv_append");
 }
 
-extern "C" int b200_attn_decode(const void* qkv, const void* kcache, const void* vcache, void* out, int B, int H, int hs,
-                                int Tmax, int len, float scale, const int* pos_dev, cudaStream_t st) {
+extern "C" int b200_attn_decode(const void* qkv, void* kcache, void* vcache, void* out, int B, int H, int hs,
+                                int Tmax, int len, float scale, const int* pos_dev, int append, cudaStream_t st) {
     B200_REQUIRE(hs == 64 || hs == 128, "attn_decode: head size must be 64 or 128");
     B200_REQUIRE(len >= 1 && len <= Tmax, "attn_decode: bad len");
     dim3 grid(H, B);
     if (hs == 64)
         B200_CHECK_CUDA(b200_launch(attn_decode_kernel<64>, dim3(grid), dim3(DEC_WARPS * 32), 0, st, (const bf16*)qkv, (const bf16*)kcache,
-                                                                (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev));
+                                                                (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev, append));
     else
         B200_CHECK_CUDA(b200_launch(attn_decode_kernel<128>, dim3(grid), dim3(DEC_WARPS * 32), 0, st, (const bf16*)qkv, (const bf16*)kcache,
-                                                                 (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev));
+                                                                 (const bf16*)vcache, (bf16*)out, H, Tmax, len, scale, pos_dev, append));
     B200_RETURN_LAUNCH_STATUS("attn_decode");
 }
 

@@ -121,8 +121,9 @@ int b200_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const f
  * KV cache layout [B, H, Tmax, hs] bf16 for k and v.  append: copies the k/v thirds of
  * qkv [B*t, 3*H*hs] into the caches at positions pos0..pos0+t-1. */
 int b200_kv_append(const void* qkv, void* kcache, void* vcache, int B, int t, int H, int hs, int Tmax, int pos0, const int* pos_dev, cudaStream_t st);
-/* single-position decode attention: q = q-third of qkv [B, 3*H*hs], attends to cache[0..len) */
-int b200_attn_decode(const void* qkv, const void* kcache, const void* vcache, void* out, int B, int H, int hs, int Tmax, int len, float scale, const int* pos_dev, cudaStream_t st);
+/* single-position decode attention: q = q-third of qkv [B, 3*H*hs], attends to cache[0..len).
+ * append != 0: first write this position's k / v thirds into the caches at index len-1 (fused kv_append). */
+int b200_attn_decode(const void* qkv, void* kcache, void* vcache, void* out, int B, int H, int hs, int Tmax, int len, float scale, const int* pos_dev, int append, cudaStream_t st);
 /* next[b] ~ softmax(logits[b, :] / temperature) restricted to the top_k largest (top_k <= 0: all);
  * Philox-free counter RNG: (seed, step, b) -> uniform.  logits bf16 [B, ld]. */
 int b200_sample(const void* logits, long long ld, long long* next, int B, int V, float temperature, int top_k, unsigned long long seed, unsigned long long step, const int* pos_dev, cudaStream_t st);

@@ -242,9 +242,9 @@ def kv_append(qkv, kcache, vcache, B, t, H, hs, Tmax, pos0=0, pos_dev=None):
          "kv_append")
 
 
-def attn_decode(qkv, kcache, vcache, out, B, H, hs, Tmax, length=1, pos_dev=None):
+def attn_decode(qkv, kcache, vcache, out, B, H, hs, Tmax, length=1, pos_dev=None, append: bool = False):
     _chk(lib.load().b200_attn_decode(_p(qkv), _p(kcache), _p(vcache), _p(out), B, H, hs, Tmax, length,
-                                     1.0 / math.sqrt(hs), _p(pos_dev), _st()), "attn_decode")
+                                     1.0 / math.sqrt(hs), _p(pos_dev), int(append), _st()), "attn_decode")
 
 
 def sample(logits, next_tok, V, temperature=1.0, seed=0, step=0, pos_dev=None):

@@ -103,8 +103,7 @@ class Generator:
                 ops.ln_fwd(db.rb, eng.P(pre + "ln1.weight"), eng.P(pre + "ln1.bias"), branch=db.mlp_out,
                            x_out=db.ra, out=db.h, want_stats=False)
             self._gemm(db, db.h, eng.W(pre + "attn.wqkv"), db.qkv)
-            ops.kv_append(db.qkv, db.kc[l], db.vc[l], B, 1, H, hs, ctx, pos_dev=db.pos)
-            ops.attn_decode(db.qkv, db.kc[l], db.vc[l], db.att, B, H, hs, ctx, pos_dev=db.pos)
+            ops.attn_decode(db.qkv, db.kc[l], db.vc[l], db.att, B, H, hs, ctx, pos_dev=db.pos, append=True)
             ops.ln_fwd(db.ra, eng.P(pre + "ln2.weight"), eng.P(pre + "ln2.bias"), branch=db.att, x_out=db.rb,
                        out=db.h, want_stats=False)
             self._gemm(db, db.h, eng.W(pre + "mlp.hidden.weight"), db.act, bias=eng.P(pre + "mlp.hidden.bias"), relu=True)

@@ -280,6 +280,13 @@ def test_decode_attention(ops, hs):
     ops.attn_decode(qkv, kc, vc, out, B, H, hs, Tmax, pos_dev=pos)
     ref = _ref_attn(hist, B, L, H, hs).view(B, L, -1)[:, -1]
     assert _rel(out, ref) < 8e-3
+    # fused append: the cache only holds L-1 positions, the kernel adds the last one itself
+    kc2, vc2 = kc.clone(), vc.clone()
+    kc2[:, :, L - 1] = 0
+    vc2[:, :, L - 1] = 0
+    out2 = torch.empty_like(out)
+    ops.attn_decode(qkv, kc2, vc2, out2, B, H, hs, Tmax, pos_dev=pos, append=True)
+    assert _rel(out2, ref) < 8e-3 and torch.equal(kc2, kc) and torch.equal(vc2, vc)
 
 
 def test_sampler_distribution(ops):
