@@ -26,6 +26,10 @@ namespace {
 constexpr int BM = 128, BN = 128;
 constexpr int SUB = 128 * 64 * 2;   // one [128 rows x 64 cols] bf16 sub-tile = 16 KiB
 constexpr int NTHREADS = 192;
+constexpr int BWD_EW_WARPS = 16;
+struct MaskOn { static constexpr bool value = true; };
+struct MaskOff { static constexpr bool value = false; };
+constexpr int NTHREADS_BWD = 64 + 32 * BWD_EW_WARPS;   // TMA warp + MMA warp + elementwise warps
 
 template <int HD> struct ACfg {
     static constexpr int NSUB = HD / 64;                 // sub-tiles per Q / K / V tile
@@ -64,7 +68,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
     if (base - ptx::smem_u32(smem_raw) > 768u) __trap();   // dynamic smem window less aligned than assumed
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int qt = gridDim.x - 1 - blockIdx.x;     // heavy (late) query tiles first
     const int h = blockIdx.y, b = blockIdx.z;
     const int q0 = qt * BM;
@@ -94,7 +98,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     __syncthreads();
     ptx::tc_fence_after();
     pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
-    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base));
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base)), 0);
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -119,7 +123,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        // whole warp converged, one elected lane issues inside the wrappers (uniform operands, see ptx.cuh)
+        {
             constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(128, 128, 0, 0);
             constexpr uint32_t idesc_pv = ptx::umma_idesc_bf16(128, HD, 0, 1);
             auto issue_s = [&](int j) {
@@ -131,10 +136,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 for (int kk = 0; kk < HD / 16; ++kk) {
                     const uint64_t ad = ptx::umma_desc(sQ + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
                     const uint64_t bd = ptx::umma_desc(sK + st * C::TILE + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
-                    ptx::mma_bf16_ss(tmem + sb * 128, ad, bd, idesc_s, kk > 0 ? 1u : 0u);
+                    ptx::mma_bf16_ss_w(tmem + sb * 128, ad, bd, idesc_s, kk > 0 ? 1u : 0u);
                 }
-                ptx::mma_commit(s_full(sb));
-                ptx::mma_commit(k_empty(st));
+                ptx::mma_commit_w(s_full(sb));
+                ptx::mma_commit_w(k_empty(st));
             };
             ptx::mbar_wait(q_full, 0);
             issue_s(0);
@@ -149,10 +154,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                     // A = P [128 q x 128 kv], K-major, two 64-wide sub-tiles; B = V [kv x hs], MN-major
                     const uint64_t ad = ptx::umma_desc(sP + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
                     const uint64_t bd = ptx::umma_desc(sV + st * C::TILE + kk * 2048, SUB, 1024);
-                    ptx::mma_bf16_ss(tmem + C::O_COL, ad, bd, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                    ptx::mma_bf16_ss_w(tmem + C::O_COL, ad, bd, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
                 }
-                ptx::mma_commit(pv_done);
-                ptx::mma_commit(v_empty(st));
+                ptx::mma_commit_w(pv_done);
+                ptx::mma_commit_w(v_empty(st));
             }
         }
     } else {
@@ -321,22 +326,43 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, floa
 // [128 x hs] with K = 64 whose B operand is the streamed tile read MN-major.  Recomputing S in the
 // second pass costs 2 extra MMAs per tile pair but removes the cross-CTA dQ reduction entirely
 // (fp32 RED traffic + a conversion pass were the bottleneck of the single-pass version).
-// hs=64: 256 TMEM columns and < 113 KB smem per CTA, so two CTAs share an SM and overlap each
-// other's MMA / exponential phases.
-// Warp roles: 0 TMA, 1 MMA, 2-5 elementwise + epilogue.
+// One CTA per SM, software-pipelined INSIDE the CTA: the score accumulators (TMEM) and the bf16 out tiles (smem)
+// are double-buffered, so while the elementwise warps work on tile n the tensor pipe runs the accumulate MMAs
+// of tile n-1 and the score MMAs of tile n+1 (issue order: scores(n+1), then acc(n) once the out tile is
+// written).  Streamed tiles are triple-buffered.  The first version ran two independent CTAs per SM instead
+// and left the tensor pipe 20% busy: every CTA spent most of its time in the serial chain MMA -> commit ->
+// wake-up -> exp -> arrive -> wake-up -> MMA (ncu: elementwise warps waiting on sc_full).
+// CTAs are ordered heaviest stationary tile first (longest-processing-time order) so the causal triangle
+// does not leave a long tail.
+// Warp roles: 0 TMA (+ per-tile lse/delta staging in the key-stationary pass), 1 MMA, 2-17 elementwise +
+// epilogue; four elementwise warps share each TMEM lane quarter and split the 64 score columns.
 // =============================================================================================
 constexpr int SUB64 = 64 * 64 * 2;     // [64 rows x 64 cols] bf16 sub-tile = 8 KiB
+
+// Optional in-kernel timeline (tools/attn_trace.cu builds this file with -DATTN_TRACE): CTA 0 records clock64()
+// at its pipeline hand-offs.  Compiled out of the library.
+#ifdef ATTN_TRACE
+__device__ long long g_attn_trace[2][3][64][8];   // [pass][role][tile][event]
+#define TRACE(role, n, k) do { if (blockIdx.x == 0 && (n) < 64) g_attn_trace[DKV ? 1 : 0][role][n][k] = clock64(); } while (0)
+#else
+#define TRACE(role, n, k) do { } while (0)
+#endif
 
 template <int HD, bool DKV> struct BCfg {
     static constexpr int NSUB = HD / 64;
     static constexpr int STAT = NSUB * SUB;                 // stationary tile [128 x HD]
     static constexpr int STR = NSUB * SUB64;                // streamed tile  [64 x HD]
+    static constexpr int NST = 3;                           // streamed stages
     static constexpr int NOUT = DKV ? 2 : 1;                // bf16 tiles produced per iteration (P^T, dS^T | dS)
     static constexpr int NACC = DKV ? 2 : 1;                // TMEM accumulators (dV, dK | dQ)
-    static constexpr int SC1 = 0, SC2 = 64, ACC = 128;      // TMEM columns
-    static constexpr int TMEM_COLS = (128 + NACC * HD) <= 256 ? 256 : 512;
-    static constexpr int USED = 2 * STAT + 2 * 2 * STR + NOUT * SUB + 1280;   // stat x2 | streamed x2 stages x2 | out | bars (128) + vec (1024)
+    static constexpr int OUT = NOUT * SUB;                  // one stage of out tiles
+    static constexpr int ACC = 256;                         // TMEM columns: scores stage s at 128*s (S | dP), then acc
+    static constexpr int TMEM_COLS = 512;
+    // stat x2 | streamed x2 tensors x NST stages | out x2 stages | barriers (256) + lse/delta staging (1024)
+    static constexpr int USED = 2 * STAT + 2 * NST * STR + 2 * OUT + 1280;
     static constexpr int SMEM = USED + 768;
+    static_assert(ACC + NACC * HD <= 512, "TMEM budget");
+    static_assert(SMEM <= 232448, "smem budget");
 };
 
 template <int HD>
@@ -362,42 +388,50 @@ __global__ void __launch_bounds__(256) attn_bwd_delta_tc_kernel(const bf16* __re
 }
 
 // tm128 / tm64: qkv viewed [B][T][3d] with 128- / 64-row boxes; tdo128 / tdo64: dO viewed [B][T][d].
+// Grid: 1-D, ntile * H * B CTAs; blockIdx.x / (H*B) is the stationary tile's rank by amount of work.
 template <int HD, bool DKV>
-__global__ void __launch_bounds__(NTHREADS, HD == 64 ? 2 : 1)
+__global__ void __launch_bounds__(NTHREADS_BWD, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm64,
                    const __grid_constant__ CUtensorMap tdo128, const __grid_constant__ CUtensorMap tdo64,
                    const float* __restrict__ lse, const float* __restrict__ delta, bf16* __restrict__ dqkv, int T, int H,
-                   float scale, float scale_log2) {
+                   int HB, int ntile, float scale, float scale_log2) {
     using C = BCfg<HD, DKV>;
+    constexpr int NST = C::NST;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t sA0 = base;                          // stationary operand of score MMA 1 (K | Q)
     const uint32_t sA1 = sA0 + C::STAT;                 // stationary operand of score MMA 2 (V | dO)
-    const uint32_t sB0 = sA1 + C::STAT;                 // streamed, 2 stages: (Q_i | K_j)
-    const uint32_t sB1 = sB0 + 2 * C::STR;              // streamed, 2 stages: (dO_i | V_j)
-    const uint32_t sOut = sB1 + 2 * C::STR;             // NOUT tiles [128 x 64] bf16
-    const uint32_t bars = sOut + C::NOUT * SUB;
+    const uint32_t sB0 = sA1 + C::STAT;                 // streamed, NST stages: (Q_i | K_j)
+    const uint32_t sB1 = sB0 + NST * C::STR;            // streamed, NST stages: (dO_i | V_j)
+    const uint32_t sOut = sB1 + NST * C::STR;           // 2 stages x NOUT tiles [128 x 64] bf16
+    const uint32_t bars = sOut + 2 * C::OUT;
     const uint32_t stat_full = bars;
     auto str_full = [&](int s) { return bars + 8u * (1 + s); };
-    auto str_empty = [&](int s) { return bars + 8u * (3 + s); };
-    const uint32_t sc_full = bars + 8u * 5, sc_empty = bars + 8u * 6;
-    const uint32_t out_full = bars + 8u * 7, out_empty = bars + 8u * 8;
-    const uint32_t acc_done = bars + 8u * 9;
-    const uint32_t tmem_slot = bars + 8u * 10;
+    auto str_empty = [&](int s) { return bars + 8u * (4 + s); };
+    auto sc_full = [&](int s) { return bars + 8u * (7 + s); };
+    auto sc_empty = [&](int s) { return bars + 8u * (9 + s); };
+    auto out_full = [&](int s) { return bars + 8u * (11 + s); };
+    auto out_empty = [&](int s) { return bars + 8u * (13 + s); };
+    auto vec_full = [&](int s) { return bars + 8u * (15 + s); };
+    const uint32_t acc_done = bars + 8u * 17;
+    const uint32_t tmem_slot = bars + 8u * 18;
     uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
-    float* s_vec = reinterpret_cast<float*>(gen + (bars + 128 - base));   // [2 stages][lse2(64) | delta(64)]
+    float* s_vec = reinterpret_cast<float*>(gen + (bars + 256 - base));   // [2 stages][lse2(64) | delta(64)]
     if (base - ptx::smem_u32(smem_raw) > 768u) __trap();
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int h = blockIdx.y, b = blockIdx.z;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
+    const int rank = (int)blockIdx.x / HB, hb = (int)blockIdx.x - rank * HB;
+    const int h = hb % H, b = hb / H;
     const int d_model = H * HD;
     const int n64 = (T + 63) / 64;
-    // stationary tile index and the range of streamed 64-row tiles
-    const int ts = DKV ? (int)blockIdx.x : (int)(gridDim.x - 1 - blockIdx.x);   // heavy tiles first in both passes
+    // stationary tile index (rank 0 = most streamed tiles) and the range of streamed 64-row tiles
+    const int ts = DKV ? rank : ntile - 1 - rank;
     const int r0 = ts * 128;                            // first key (DKV) / query (DQ) row of the stationary tile
     const int it0 = DKV ? 2 * ts : 0;                   // first streamed tile
     const int it1 = DKV ? n64 : min(n64, 2 * ts + 2);   // one past the last streamed tile
     const int niter = it1 - it0;
+    const float* lse_g = lse + ((size_t)b * H + h) * T;
+    const float* del_g = delta + ((size_t)b * H + h) * T;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm128); ptx::prefetch_tmap(&tm64);
@@ -405,9 +439,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
     }
     if (warp == 1 && lane == 0) {
         ptx::mbar_init(stat_full, 1);
-        for (int s = 0; s < 2; ++s) { ptx::mbar_init(str_full(s), 1); ptx::mbar_init(str_empty(s), 1); }
-        ptx::mbar_init(sc_full, 1);   ptx::mbar_init(sc_empty, 4);
-        ptx::mbar_init(out_full, 4);  ptx::mbar_init(out_empty, 1);
+        for (int s = 0; s < NST; ++s) { ptx::mbar_init(str_full(s), 1); ptx::mbar_init(str_empty(s), 1); }
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(sc_full(s), 1);   ptx::mbar_init(sc_empty(s), BWD_EW_WARPS);
+            ptx::mbar_init(out_full(s), BWD_EW_WARPS);  ptx::mbar_init(out_empty(s), 1);
+            ptx::mbar_init(vec_full(s), 1);
+        }
         ptx::mbar_init(acc_done, 1);
         ptx::fence_mbar_init();
     }
@@ -419,198 +456,243 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
     __syncthreads();
     ptx::tc_fence_after();
     pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
-    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base));
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base)), 0);
 
     if (warp == 0) {
-        // ------------------------------------------------------------------ TMA producer
-        if (lane == 0 && niter > 0) {
-            ptx::mbar_arrive_expect_tx(stat_full, 2 * C::STAT);
-#pragma unroll
-            for (int c = 0; c < C::NSUB; ++c) {
-                if (DKV) {
-                    ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, d_model + h * HD + c * 64, r0, b);        // K
-                    ptx::tma_load_3d(sA1 + c * SUB, &tm128, stat_full, 2 * d_model + h * HD + c * 64, r0, b);    // V
-                } else {
-                    ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, h * HD + c * 64, r0, b);                  // Q
-                    ptx::tma_load_3d(sA1 + c * SUB, &tdo128, stat_full, h * HD + c * 64, r0, b);                 // dO
-                }
-            }
-            for (int n = 0; n < niter; ++n) {
-                const int st = n & 1;
-                const int row0 = (it0 + n) * 64;
-                ptx::mbar_wait(str_empty(st), ((n >> 1) & 1) ^ 1);
-                ptx::mbar_arrive_expect_tx(str_full(st), 2 * C::STR);
+        // ------------------------------------------------------------------ TMA producer (lane 0) + statistics staging
+        if (niter > 0) {
+            if (lane == 0) {
+                ptx::mbar_arrive_expect_tx(stat_full, 2 * C::STAT);
 #pragma unroll
                 for (int c = 0; c < C::NSUB; ++c) {
                     if (DKV) {
-                        ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), h * HD + c * 64, row0, b);    // Q_i
-                        ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tdo64, str_full(st), h * HD + c * 64, row0, b);   // dO_i
+                        ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, d_model + h * HD + c * 64, r0, b);        // K
+                        ptx::tma_load_3d(sA1 + c * SUB, &tm128, stat_full, 2 * d_model + h * HD + c * 64, r0, b);    // V
                     } else {
-                        ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), d_model + h * HD + c * 64, row0, b);      // K_j
-                        ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tm64, str_full(st), 2 * d_model + h * HD + c * 64, row0, b);  // V_j
+                        ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, h * HD + c * 64, r0, b);                  // Q
+                        ptx::tma_load_3d(sA1 + c * SUB, &tdo128, stat_full, h * HD + c * 64, r0, b);                 // dO
                     }
+                }
+            }
+            for (int n = 0; n < niter; ++n) {
+                const int st = n % NST;
+                const int row0 = (it0 + n) * 64;
+                if (lane == 0) {
+                    ptx::mbar_wait(str_empty(st), ((n / NST) & 1) ^ 1);
+                    TRACE(0, n, 0);
+                    ptx::mbar_arrive_expect_tx(str_full(st), 2 * C::STR);
+#pragma unroll
+                    for (int c = 0; c < C::NSUB; ++c) {
+                        if (DKV) {
+                            ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), h * HD + c * 64, row0, b);    // Q_i
+                            ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tdo64, str_full(st), h * HD + c * 64, row0, b);   // dO_i
+                        } else {
+                            ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), d_model + h * HD + c * 64, row0, b);      // K_j
+                            ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tm64, str_full(st), 2 * d_model + h * HD + c * 64, row0, b);  // V_j
+                        }
+                    }
+                }
+                if (DKV) {
+                    // per-column (query) statistics of streamed tile n -> smem stage n&1.  The stage is free once
+                    // every elementwise warp has finished tile n-2, which is what out_full(n-2) says.
+                    const int s = n & 1;
+                    __syncwarp();
+                    if (n >= 2) ptx::mbar_wait(out_full(s), ((n - 2) >> 1) & 1);
+                    float* v = s_vec + s * 128;
+                    const int q0 = row0 + lane, q1 = row0 + 32 + lane;
+                    v[lane] = q0 < T ? lse_g[q0] * 1.4426950408889634f : INFINITY;
+                    v[32 + lane] = q1 < T ? lse_g[q1] * 1.4426950408889634f : INFINITY;
+                    v[64 + lane] = q0 < T ? del_g[q0] : 0.f;
+                    v[96 + lane] = q1 < T ? del_g[q1] : 0.f;
+                    __syncwarp();
+                    if (lane == 0) { ptx::mbar_arrive(vec_full(s)); TRACE(0, n, 1); }
                 }
             }
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (lane == 0 && niter > 0) {
+        // The whole warp runs this loop converged (uniform operands -> no per-MMA R2UR loops, see ptx.cuh); one
+        // elected lane issues inside each wrapper.
+        if (niter > 0) {
             constexpr uint32_t id_sc = ptx::umma_idesc_bf16(128, 64, 0, 0);     // scores: both operands K-major
             constexpr uint32_t id_acc = ptx::umma_idesc_bf16(128, HD, 0, 1);    // accumulate: A K-major (smem out tile), B MN-major
-            ptx::mbar_wait(stat_full, 0);
-            for (int n = 0; n < niter; ++n) {
-                const int st = n & 1;
-                const uint32_t b0 = sB0 + st * C::STR, b1 = sB1 + st * C::STR;
-                ptx::mbar_wait(str_full(st), (n >> 1) & 1);
-                ptx::mbar_wait(sc_empty, (n & 1) ^ 1);
+            auto accumulate = [&](int m) {
+                const int sm = m & 1, stm = m % NST;
+                const uint32_t b0 = sB0 + stm * C::STR, b1 = sB1 + stm * C::STR, so = sOut + sm * C::OUT;
+                ptx::mbar_wait(out_full(sm), (m >> 1) & 1);
                 ptx::tc_fence_after();
-#pragma unroll
-                for (int kk = 0; kk < HD / 16; ++kk) {
-                    const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
-                    ptx::mma_bf16_ss(tmem + C::SC1, ptx::umma_desc(sA0 + oa, 16, 1024), ptx::umma_desc(b0 + ob, 16, 1024),
-                                     id_sc, kk > 0 ? 1u : 0u);
-                }
-#pragma unroll
-                for (int kk = 0; kk < HD / 16; ++kk) {
-                    const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
-                    ptx::mma_bf16_ss(tmem + C::SC2, ptx::umma_desc(sA1 + oa, 16, 1024), ptx::umma_desc(b1 + ob, 16, 1024),
-                                     id_sc, kk > 0 ? 1u : 0u);
-                }
-                ptx::mma_commit(sc_full);
-                ptx::mbar_wait(out_full, n & 1);
-                ptx::tc_fence_after();
+                TRACE(1, m, 3);
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {                 // contraction over the 64 streamed rows
-                    const uint32_t acc = (n > 0 || kk > 0) ? 1u : 0u;
+                    const uint32_t acc = (m > 0 || kk > 0) ? 1u : 0u;
                     if (DKV) {
                         // dV += P^T dO_i ; dK += dS^T Q_i
-                        ptx::mma_bf16_ss(tmem + C::ACC, ptx::umma_desc(sOut + kk * 32, 16, 1024),
+                        ptx::mma_bf16_ss_w(tmem + C::ACC, ptx::umma_desc(so + kk * 32, 16, 1024),
                                          ptx::umma_desc(b1 + kk * 2048, SUB64, 1024), id_acc, acc);
-                        ptx::mma_bf16_ss(tmem + C::ACC + HD, ptx::umma_desc(sOut + SUB + kk * 32, 16, 1024),
+                        ptx::mma_bf16_ss_w(tmem + C::ACC + HD, ptx::umma_desc(so + SUB + kk * 32, 16, 1024),
                                          ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
                     } else {
                         // dQ += dS K_j
-                        ptx::mma_bf16_ss(tmem + C::ACC, ptx::umma_desc(sOut + kk * 32, 16, 1024),
+                        ptx::mma_bf16_ss_w(tmem + C::ACC, ptx::umma_desc(so + kk * 32, 16, 1024),
                                          ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
                     }
                 }
-                ptx::mma_commit(out_empty);
-                ptx::mma_commit(str_empty(st));
+                ptx::mma_commit_w(out_empty(sm));
+                ptx::mma_commit_w(str_empty(stm));
+                TRACE(1, m, 4);
+            };
+            ptx::mbar_wait(stat_full, 0);
+            for (int n = 0; n < niter; ++n) {
+                // scores of tile n first, so they run while the elementwise warps are still on tile n-1 ...
+                const int st = n % NST, s = n & 1;
+                const uint32_t b0 = sB0 + st * C::STR, b1 = sB1 + st * C::STR;
+                ptx::mbar_wait(str_full(st), (n / NST) & 1);
+                TRACE(1, n, 0);
+                ptx::mbar_wait(sc_empty(s), ((n >> 1) & 1) ^ 1);
+                ptx::tc_fence_after();
+                TRACE(1, n, 1);
+#pragma unroll
+                for (int kk = 0; kk < HD / 16; ++kk) {
+                    const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
+                    ptx::mma_bf16_ss_w(tmem + s * 128, ptx::umma_desc(sA0 + oa, 16, 1024), ptx::umma_desc(b0 + ob, 16, 1024),
+                                     id_sc, kk > 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int kk = 0; kk < HD / 16; ++kk) {
+                    const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
+                    ptx::mma_bf16_ss_w(tmem + s * 128 + 64, ptx::umma_desc(sA1 + oa, 16, 1024), ptx::umma_desc(b1 + ob, 16, 1024),
+                                     id_sc, kk > 0 ? 1u : 0u);
+                }
+                ptx::mma_commit_w(sc_full(s));
+                TRACE(1, n, 2);
+                // ... then the accumulation of tile n-1, whose out tiles they have just finished
+                if (n > 0) accumulate(n - 1);
             }
-            ptx::mma_commit(acc_done);
+            accumulate(niter - 1);
+            ptx::mma_commit_w(acc_done);
         }
     } else {
-        // ------------------------------------------------------------------ elementwise warps (2..5): thread = stationary row
+        // ------------------------------------------------------------------ elementwise warps (2..17)
+        // NPART warps share each TMEM lane quarter (tcgen05.ld reaches lanes 32*(warp%4)..+31): thread = stationary
+        // row, `part` = which slice of the 64 score columns.  The backward needs no row reductions (lse and delta
+        // are inputs), so the column split is free; 4 warps per scheduler hide the exp2 / LDS latencies.
+        constexpr int NPART = BWD_EW_WARPS / 4, CPW = 64 / NPART;   // column parts per lane quarter, columns per warp
         const int q = warp & 3;
+        const int part = (warp - 2) >> 2;
         const int row = q * 32 + lane;
         const int srow = r0 + row;                                  // key row (DKV) / query row (DQ)
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-        const float* lse_g = lse + ((size_t)b * H + h) * T;
-        const float* del_g = delta + ((size_t)b * H + h) * T;
         float my_l2 = INFINITY, my_dl = 0.f;
         if (!DKV && srow < T) { my_l2 = lse_g[srow] * 1.4426950408889634f; my_dl = del_g[srow]; }
-        const int t128 = threadIdx.x - 64;                          // 0..127 among the elementwise threads
         for (int n = 0; n < niter; ++n) {
+            const int s = n & 1, ph = (n >> 1) & 1;
             const int c0 = (it0 + n) * 64;                          // first streamed row = first score column
-            if (DKV) {
-                // per-column (query) statistics of this tile -> smem, double-buffered by parity
-                float* v = s_vec + (n & 1) * 128;
-                const int qq = c0 + (t128 & 63);
-                if (t128 < 64) v[t128] = qq < T ? lse_g[qq] * 1.4426950408889634f : INFINITY;
-                else v[t128] = qq < T ? del_g[qq] : 0.f;
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-            }
-            const float* vl = s_vec + (n & 1) * 128;
+            const float* vl = s_vec + s * 128;
             // causal mask is needed only where the streamed tile overlaps the diagonal
             const bool need_mask = DKV ? (c0 < r0 + 128) : (c0 + 63 > r0);
-            ptx::mbar_wait(sc_full, n & 1);
+            if (warp == 2 && lane == 0) TRACE(2, n, 0);
+            if (DKV) ptx::mbar_wait(vec_full(s), ph);
+            if (warp == 2 && lane == 0) TRACE(2, n, 1);
+            ptx::mbar_wait(sc_full(s), ph);
             ptx::tc_fence_after();
-            ptx::mbar_wait(out_empty, (n & 1) ^ 1);
-#pragma unroll 1
-            for (int c = 0; c < 2; ++c) {
-                uint32_t rs[32], rp[32];
-                ptx::tmem_ld_32x32(tmem + lane_off + C::SC1 + c * 32, rs);
-                ptx::tmem_ld_32x32(tmem + lane_off + C::SC2 + c * 32, rp);
-                ptx::tmem_ld_wait();
-                if (c == 1) {
-                    // both score tiles are in registers: the MMA warp may overwrite them
-                    ptx::tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(sc_empty);
-                }
-                uint32_t pk[16], dk[16];
+            if (warp == 2 && lane == 0) TRACE(2, n, 2);
+            ptx::mbar_wait(out_empty(s), ph ^ 1);
+            if (warp == 2 && lane == 0) TRACE(2, n, 3);
+            const uint32_t dst = sOut + s * C::OUT + row * 128;
+            // MASKED is a compile-time flag so the 7-of-9 off-diagonal tiles carry no compare/select instructions
+            auto tile = [&](auto masked_tag) {
+                constexpr bool MASKED = decltype(masked_tag)::value;
 #pragma unroll
-                for (int e = 0; e < 32; e += 2) {
-                    const int col = c * 32 + e;
-                    const float l2a = DKV ? vl[col] : my_l2, l2b = DKV ? vl[col + 1] : my_l2;
-                    const float dla = DKV ? vl[64 + col] : my_dl, dlb = DKV ? vl[64 + col + 1] : my_dl;
-                    float p0 = exp2f(__uint_as_float(rs[e]) * scale_log2 - l2a);
-                    float p1 = exp2f(__uint_as_float(rs[e + 1]) * scale_log2 - l2b);
-                    if (need_mask) {
-                        // key index must be <= query index
-                        const int key0 = DKV ? srow : c0 + col, qry0 = DKV ? c0 + col : srow;
-                        const int key1 = DKV ? srow : key0 + 1, qry1 = DKV ? qry0 + 1 : srow;
-                        if (key0 > qry0) p0 = 0.f;
-                        if (key1 > qry1) p1 = 0.f;
+                for (int c = 0; c < CPW / 16; ++c) {
+                    const int cb = part * CPW + c * 16;             // first score column of this 16-wide piece
+                    uint32_t rs[16], rp[16];
+                    ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + cb, rs);
+                    ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + 64 + cb, rp);
+                    ptx::tmem_ld_wait();
+                    if (c == CPW / 16 - 1) {
+                        // this warp's share of both score tiles is in registers: the MMA warp may overwrite it
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(sc_empty(s));
                     }
-                    if (DKV ? (srow >= T) : (c0 + col >= T)) p0 = 0.f;          // zero-filled key rows
-                    if (DKV ? (srow >= T) : (c0 + col + 1 >= T)) p1 = 0.f;
-                    const float s0 = p0 * (__uint_as_float(rp[e]) - dla) * scale;
-                    const float s1 = p1 * (__uint_as_float(rp[e + 1]) - dlb) * scale;
-                    pk[e >> 1] = pack_bf16x2(p0, p1);
-                    dk[e >> 1] = pack_bf16x2(s0, s1);
-                }
-                const uint32_t dst = sOut + row * 128;
+                    uint32_t pk[8], dk[8];
 #pragma unroll
-                for (int ch = 0; ch < 4; ++ch) {
-                    const uint32_t sw = (((uint32_t)(c * 4 + ch)) ^ ((uint32_t)row & 7u)) << 4;
-                    if (DKV) {
-                        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]),
-                                     "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3]) : "memory");
-                        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + SUB + sw), "r"(dk[4 * ch]),
-                                     "r"(dk[4 * ch + 1]), "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
-                    } else {
-                        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(dk[4 * ch]), "r"(dk[4 * ch + 1]),
-                                     "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
+                    for (int e = 0; e < 16; e += 2) {
+                        const int col = cb + e;
+                        const float l2a = DKV ? vl[col] : my_l2, l2b = DKV ? vl[col + 1] : my_l2;
+                        const float dla = DKV ? vl[64 + col] : my_dl, dlb = DKV ? vl[64 + col + 1] : my_dl;
+                        // Rows / columns past T need no extra test: TMA zero-fills them, out-of-range QUERIES carry
+                        // lse = +inf (p = 0), and out-of-range KEYS are either masked by causality or only feed
+                        // output rows that are never stored.
+                        float p0 = exp2f(__uint_as_float(rs[e]) * scale_log2 - l2a);
+                        float p1 = exp2f(__uint_as_float(rs[e + 1]) * scale_log2 - l2b);
+                        if (MASKED) {
+                            // key index must be <= query index
+                            const int key0 = DKV ? srow : c0 + col, qry0 = DKV ? c0 + col : srow;
+                            if (key0 > qry0) p0 = 0.f;
+                            if (DKV ? (key0 > qry0 + 1) : (key0 + 1 > qry0)) p1 = 0.f;
+                        }
+                        // the 1/sqrt(hs) factor of dS is applied once per output element in the epilogue
+                        const float s0 = p0 * (__uint_as_float(rp[e]) - dla);
+                        const float s1 = p1 * (__uint_as_float(rp[e + 1]) - dlb);
+                        if (DKV) pk[e >> 1] = pack_bf16x2(p0, p1);
+                        dk[e >> 1] = pack_bf16x2(s0, s1);
+                    }
+#pragma unroll
+                    for (int ch = 0; ch < 2; ++ch) {
+                        const uint32_t sw = (((uint32_t)(cb / 8 + ch)) ^ ((uint32_t)row & 7u)) << 4;
+                        if (DKV) {
+                            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]),
+                                         "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3]) : "memory");
+                            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + SUB + sw), "r"(dk[4 * ch]),
+                                         "r"(dk[4 * ch + 1]), "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
+                        } else {
+                            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(dk[4 * ch]), "r"(dk[4 * ch + 1]),
+                                         "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
+                        }
                     }
                 }
-            }
+            };
+            if (need_mask) tile(MaskOn{}); else tile(MaskOff{});
+            if (warp == 2 && lane == 0) TRACE(2, n, 4);
             ptx::fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(out_full);
+            if (lane == 0) ptx::mbar_arrive(out_full(s));
+            if (warp == 2 && lane == 0) TRACE(2, n, 5);
         }
-        // ---- epilogue: accumulator rows -> bf16 -> dqkv (thread = stationary row)
+        // ---- epilogue: accumulator rows -> bf16 -> dqkv (thread = stationary row, warp half = alternate 16-col pieces)
         if (niter > 0) {
             ptx::mbar_wait(acc_done, 0);
             ptx::tc_fence_after();
         }
         bf16* g0 = dqkv + ((size_t)b * T + srow) * (3 * d_model) + h * HD + (DKV ? 2 * d_model : 0);   // dV | dQ
         bf16* g1 = dqkv + ((size_t)b * T + srow) * (3 * d_model) + h * HD + d_model;                    // dK
+        const float f0 = DKV ? 1.f : scale;
 #pragma unroll 1
-        for (int c = 0; c < HD / 32; ++c) {
-            uint32_t r0v[32], r1v[32];
+        for (int c = part; c < HD / 16; c += NPART) {
+            uint32_t r0v[16], r1v[16];
             if (niter > 0) {
-                ptx::tmem_ld_32x32(tmem + lane_off + C::ACC + c * 32, r0v);
-                if (DKV) ptx::tmem_ld_32x32(tmem + lane_off + C::ACC + HD + c * 32, r1v);
+                ptx::tmem_ld_32x16(tmem + lane_off + C::ACC + c * 16, r0v);
+                if (DKV) ptx::tmem_ld_32x16(tmem + lane_off + C::ACC + HD + c * 16, r1v);
                 ptx::tmem_ld_wait();
             } else {
 #pragma unroll
-                for (int e = 0; e < 32; ++e) { r0v[e] = 0u; r1v[e] = 0u; }
+                for (int e = 0; e < 16; ++e) { r0v[e] = 0u; r1v[e] = 0u; }
             }
             if (srow < T) {
 #pragma unroll
-                for (int e = 0; e < 32; e += 8) {
-                    *reinterpret_cast<uint4*>(g0 + c * 32 + e) =
-                        make_uint4(pack_bf16x2(__uint_as_float(r0v[e]), __uint_as_float(r0v[e + 1])),
-                                   pack_bf16x2(__uint_as_float(r0v[e + 2]), __uint_as_float(r0v[e + 3])),
-                                   pack_bf16x2(__uint_as_float(r0v[e + 4]), __uint_as_float(r0v[e + 5])),
-                                   pack_bf16x2(__uint_as_float(r0v[e + 6]), __uint_as_float(r0v[e + 7])));
+                for (int e = 0; e < 16; e += 8) {
+                    *reinterpret_cast<uint4*>(g0 + c * 16 + e) =
+                        make_uint4(pack_bf16x2(f0 * __uint_as_float(r0v[e]), f0 * __uint_as_float(r0v[e + 1])),
+                                   pack_bf16x2(f0 * __uint_as_float(r0v[e + 2]), f0 * __uint_as_float(r0v[e + 3])),
+                                   pack_bf16x2(f0 * __uint_as_float(r0v[e + 4]), f0 * __uint_as_float(r0v[e + 5])),
+                                   pack_bf16x2(f0 * __uint_as_float(r0v[e + 6]), f0 * __uint_as_float(r0v[e + 7])));
                     if (DKV)
-                        *reinterpret_cast<uint4*>(g1 + c * 32 + e) =
-                            make_uint4(pack_bf16x2(__uint_as_float(r1v[e]), __uint_as_float(r1v[e + 1])),
-                                       pack_bf16x2(__uint_as_float(r1v[e + 2]), __uint_as_float(r1v[e + 3])),
-                                       pack_bf16x2(__uint_as_float(r1v[e + 4]), __uint_as_float(r1v[e + 5])),
-                                       pack_bf16x2(__uint_as_float(r1v[e + 6]), __uint_as_float(r1v[e + 7])));
+                        *reinterpret_cast<uint4*>(g1 + c * 16 + e) =
+                            make_uint4(pack_bf16x2(scale * __uint_as_float(r1v[e]), scale * __uint_as_float(r1v[e + 1])),
+                                       pack_bf16x2(scale * __uint_as_float(r1v[e + 2]), scale * __uint_as_float(r1v[e + 3])),
+                                       pack_bf16x2(scale * __uint_as_float(r1v[e + 4]), scale * __uint_as_float(r1v[e + 5])),
+                                       pack_bf16x2(scale * __uint_as_float(r1v[e + 6]), scale * __uint_as_float(r1v[e + 7])));
                 }
             }
         }
@@ -633,9 +715,9 @@ int launch_bwd_pass(const CUtensorMap& t128, const CUtensorMap& t64, const CUten
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
         cfg = true;
     }
-    dim3 grid((T + 127) / 128, H, B);
-    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NTHREADS), C::SMEM, st, t128, t64, d128, d64, lse, delta, (bf16*)dqkv, T, H, scale,
-                                          scale * 1.4426950408889634f));
+    const int ntile = (T + 127) / 128;
+    B200_CHECK_CUDA(b200_launch(kern, dim3(ntile * H * B), dim3(NTHREADS_BWD), C::SMEM, st, t128, t64, d128, d64, lse, delta,
+                                (bf16*)dqkv, T, H, H * B, ntile, scale, scale * 1.4426950408889634f));
     return 0;
 }
 

@@ -60,7 +60,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));  // generic pointer to aligned base
     float* s_bias = reinterpret_cast<float*>(smem_gen + (bar_base + 256 - smem_base));   // [256] bias of the current tile
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA);
@@ -86,7 +86,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     __syncthreads();
     ptx::tc_fence_after();
     pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
-    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)), 0);
 
     const int ntiles = p.num_m * p.num_n;
     const int nunits = ntiles * p.splits;
@@ -126,7 +126,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        // whole warp converged, one elected lane issues inside the wrappers (uniform operands, see ptx.cuh)
+        {
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             // K-major, 128B swizzle: 8-row groups 1024 B apart (SBO); LBO unused.
             // MN-major, 128B swizzle: 64-element MN chunks 8192 B apart (LBO), 8-k-row groups 1024 B apart (SBO).
@@ -152,14 +153,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     const uint64_t bdesc = ptx::umma_desc(sb, B_LBO, 1024);
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
-                        ptx::mma_bf16_ss(tmem_d, adesc + (uint64_t)((k * A_KSTEP) >> 4),
+                        ptx::mma_bf16_ss_w(tmem_d, adesc + (uint64_t)((k * A_KSTEP) >> 4),
                                          bdesc + (uint64_t)((k * B_KSTEP) >> 4), idesc,
                                          (kb > kb0 || k > 0) ? 1u : 0u);
                     }
-                    ptx::mma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+                    ptx::mma_commit_w(empty_bar(stage));  // frees the smem slot when these MMAs retire
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
-                ptx::mma_commit(tfull_bar(acc));        // accumulator complete -> epilogue
+                ptx::mma_commit_w(tfull_bar(acc));        // accumulator complete -> epilogue
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }

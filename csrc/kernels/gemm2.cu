@@ -63,7 +63,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
     float* s_bias = reinterpret_cast<float*>(smem_gen + (bar_base + 256 - smem_base));
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const uint32_t rank = ptx::cluster_ctarank();      // 0 = leader
     const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
 
@@ -92,7 +92,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     __syncthreads();
     ptx::tc_fence_after();
     pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
-    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)), 0);
 
     const int ntiles = p.num_m * p.num_n;        // num_m counts 256-row tiles here
     const int nunits = ntiles * p.splits;
@@ -149,7 +149,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (leader CTA only)
-        if (lane == 0 && rank == 0) {
+        // whole warp converged, one elected lane issues inside the wrappers (uniform operands, see ptx.cuh)
+        if (rank == 0) {
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(256, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             constexpr uint32_t A_LBO = A_MN ? 8192 : 16, B_LBO = B_MN ? 8192 : 16;
             constexpr uint32_t A_KSTEP = A_MN ? 2048 : 32, B_KSTEP = B_MN ? 2048 : 32;
@@ -173,14 +174,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     const uint64_t bdesc = ptx::umma_desc(sb, B_LBO, 1024);
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
-                        ptx::mma_bf16_ss_2sm(tmem_d, adesc + (uint64_t)((k * A_KSTEP) >> 4),
+                        ptx::mma_bf16_ss_2sm_w(tmem_d, adesc + (uint64_t)((k * A_KSTEP) >> 4),
                                              bdesc + (uint64_t)((k * B_KSTEP) >> 4), idesc,
                                              (kb > kb0 || k > 0) ? 1u : 0u);
                     }
-                    ptx::mma_commit_2sm(empty_bar(stage), 3);    // slot free in both CTAs
+                    ptx::mma_commit_2sm_w(empty_bar(stage), 3);    // slot free in both CTAs
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
-                ptx::mma_commit_2sm(tfull_bar(acc), 3);          // accumulators complete in both CTAs
+                ptx::mma_commit_2sm_w(tfull_bar(acc), 3);          // accumulators complete in both CTAs
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }

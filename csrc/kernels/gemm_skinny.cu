@@ -52,7 +52,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 1);
     uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int n_tile = blockIdx.x, split = blockIdx.y;
     const int n0 = n_tile * 128;
     const int kb0 = split * p.kb_per_split;
@@ -75,7 +75,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     __syncthreads();
     ptx::tc_fence_after();
     pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
-    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)), 0);
 
     if (warp == 0) {
         if (lane == 0) {
@@ -91,7 +91,8 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        // whole warp converged, one elected lane issues inside the wrappers (uniform operands, see ptx.cuh)
+        {
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, NB, 0, 0);
             int stage = 0;
             uint32_t phase = 0;
@@ -103,11 +104,11 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
                 const uint64_t bdesc = ptx::umma_desc(sa + A_BYTES, 16, 1024);
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k)
-                    ptx::mma_bf16_ss(tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-                ptx::mma_commit(empty_bar(stage));
+                    ptx::mma_bf16_ss_w(tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                ptx::mma_commit_w(empty_bar(stage));
                 if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
             }
-            ptx::mma_commit(done_bar);
+            ptx::mma_commit_w(done_bar);
         }
     } else {
         // epilogue: thread = weight row n (TMEM lane), NB accumulator columns = batch rows
