@@ -102,23 +102,24 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
-            ptx::mbar_arrive_expect_tx(q_full, C::TILE);
+        // whole warp converged; one elected lane executes each wrapper (uniform operands, see ptx.cuh)
+        {
+            ptx::mbar_arrive_expect_tx_w(q_full, C::TILE);
 #pragma unroll
-            for (int c = 0; c < C::NSUB; ++c) ptx::tma_load_3d(sQ + c * SUB, &tmQKV, q_full, h * HD + c * 64, q0, b);
+            for (int c = 0; c < C::NSUB; ++c) ptx::tma_load_3d_w(sQ + c * SUB, &tmQKV, q_full, h * HD + c * 64, q0, b);
             for (int j = 0; j < ntiles; ++j) {
                 const int st = j & 1;
                 const uint32_t ph = ((j >> 1) & 1) ^ 1;
                 ptx::mbar_wait(k_empty(st), ph);
-                ptx::mbar_arrive_expect_tx(k_full(st), C::TILE);
+                ptx::mbar_arrive_expect_tx_w(k_full(st), C::TILE);
 #pragma unroll
                 for (int c = 0; c < C::NSUB; ++c)
-                    ptx::tma_load_3d(sK + st * C::TILE + c * SUB, &tmQKV, k_full(st), d_model + h * HD + c * 64, j * BN, b);
+                    ptx::tma_load_3d_w(sK + st * C::TILE + c * SUB, &tmQKV, k_full(st), d_model + h * HD + c * 64, j * BN, b);
                 ptx::mbar_wait(v_empty(st), ph);
-                ptx::mbar_arrive_expect_tx(v_full(st), C::TILE);
+                ptx::mbar_arrive_expect_tx_w(v_full(st), C::TILE);
 #pragma unroll
                 for (int c = 0; c < C::NSUB; ++c)
-                    ptx::tma_load_3d(sV + st * C::TILE + c * SUB, &tmQKV, v_full(st), 2 * d_model + h * HD + c * 64, j * BN, b);
+                    ptx::tma_load_3d_w(sV + st * C::TILE + c * SUB, &tmQKV, v_full(st), 2 * d_model + h * HD + c * 64, j * BN, b);
             }
         }
     } else if (warp == 1) {
@@ -352,39 +353,43 @@ template <int HD, bool DKV> struct BCfg {
     static constexpr int NSUB = HD / 64;
     static constexpr int STAT = NSUB * SUB;                 // stationary tile [128 x HD]
     static constexpr int STR = NSUB * SUB64;                // streamed tile  [64 x HD]
-    static constexpr int NST = 3;                           // streamed stages
-    static constexpr int NOUT = DKV ? 2 : 1;                // bf16 tiles produced per iteration (P^T, dS^T | dS)
+    static constexpr int NST = HD == 64 ? 6 : 4;            // streamed stages (TMA latency from a cold L2 is ~2000 clk)
     static constexpr int NACC = DKV ? 2 : 1;                // TMEM accumulators (dV, dK | dQ)
-    static constexpr int OUT = NOUT * SUB;                  // one stage of out tiles
     static constexpr int ACC = 256;                         // TMEM columns: scores stage s at 128*s (S | dP), then acc
     static constexpr int TMEM_COLS = 512;
-    // stat x2 | streamed x2 tensors x NST stages | out x2 stages | barriers (256) + lse/delta staging (1024)
-    static constexpr int USED = 2 * STAT + 2 * NST * STR + 2 * OUT + 1280;
+    // stat x2 | streamed x2 tensors x NST stages | barriers (256) + lse/delta staging (512 per stage)
+    static constexpr int USED = 2 * STAT + 2 * NST * STR + 256 + NST * 512;
     static constexpr int SMEM = USED + 768;
     static_assert(ACC + NACC * HD <= 512, "TMEM budget");
     static_assert(SMEM <= 232448, "smem budget");
 };
 
+// delta[b][h][t] = sum_c out[b][t][h][c] * dout[b][t][h][c].  16-byte loads: HD/8 lanes per (row, head).
 template <int HD>
 __global__ void __launch_bounds__(256) attn_bwd_delta_tc_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout,
                                                                float* __restrict__ delta, int B, int T, int H) {
     pdl_sync();
-    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (gw >= B * T * H) return;
-    const int h = gw % H, m = gw / H;
-    const size_t off = (size_t)m * (H * HD) + h * HD + lane * (HD / 32);
-    float s;
-    if (HD == 64) {
-        float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(out + off));
-        float2 d = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(dout + off));
-        s = a.x * d.x + a.y * d.y;
-    } else {
-        uint2 ua = *reinterpret_cast<const uint2*>(out + off), ud = *reinterpret_cast<const uint2*>(dout + off);
-        float2 a0 = unpack_bf16x2(ua.x), a1 = unpack_bf16x2(ua.y), d0 = unpack_bf16x2(ud.x), d1 = unpack_bf16x2(ud.y);
-        s = a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y;
+    constexpr int LPR = HD / 8;                               // lanes per (row, head)
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long item = gid / LPR;                         // (m, h) flattened: m * H + h
+    const int sub = (int)(gid % LPR);
+    const long long nitem = (long long)B * T * H;
+    float s = 0.f;
+    if (item < nitem) {
+        const size_t off = (size_t)item * HD + sub * 8;       // [B*T][H][HD] is contiguous in (m, h, c)
+        const uint4 ua = ldg_stream_u4(reinterpret_cast<const uint4*>(out + off));
+        const uint4 ud = ldg_stream_u4(reinterpret_cast<const uint4*>(dout + off));
+        const float2 a0 = unpack_bf16x2(ua.x), a1 = unpack_bf16x2(ua.y), a2 = unpack_bf16x2(ua.z), a3 = unpack_bf16x2(ua.w);
+        const float2 d0 = unpack_bf16x2(ud.x), d1 = unpack_bf16x2(ud.y), d2 = unpack_bf16x2(ud.z), d3 = unpack_bf16x2(ud.w);
+        s = a0.x * d0.x + a0.y * d0.y + a1.x * d1.x + a1.y * d1.y + a2.x * d2.x + a2.y * d2.y + a3.x * d3.x + a3.y * d3.y;
     }
-    s = warp_sum(s);
-    if (lane == 0) delta[((size_t)(m / T) * H + h) * T + (m % T)] = s;
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (item < nitem && sub == 0) {
+        const int h = (int)(item % H);
+        const long long m = item / H;
+        delta[((size_t)(m / T) * H + h) * T + (m % T)] = s;
+    }
 }
 
 // tm128 / tm64: qkv viewed [B][T][3d] with 128- / 64-row boxes; tdo128 / tdo64: dO viewed [B][T][d].
@@ -403,20 +408,18 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
     const uint32_t sA1 = sA0 + C::STAT;                 // stationary operand of score MMA 2 (V | dO)
     const uint32_t sB0 = sA1 + C::STAT;                 // streamed, NST stages: (Q_i | K_j)
     const uint32_t sB1 = sB0 + NST * C::STR;            // streamed, NST stages: (dO_i | V_j)
-    const uint32_t sOut = sB1 + NST * C::STR;           // 2 stages x NOUT tiles [128 x 64] bf16
-    const uint32_t bars = sOut + 2 * C::OUT;
+    const uint32_t bars = sB1 + NST * C::STR;
     const uint32_t stat_full = bars;
-    auto str_full = [&](int s) { return bars + 8u * (1 + s); };
-    auto str_empty = [&](int s) { return bars + 8u * (4 + s); };
-    auto sc_full = [&](int s) { return bars + 8u * (7 + s); };
-    auto sc_empty = [&](int s) { return bars + 8u * (9 + s); };
-    auto out_full = [&](int s) { return bars + 8u * (11 + s); };
-    auto out_empty = [&](int s) { return bars + 8u * (13 + s); };
-    auto vec_full = [&](int s) { return bars + 8u * (15 + s); };
-    const uint32_t acc_done = bars + 8u * 17;
-    const uint32_t tmem_slot = bars + 8u * 18;
+    auto str_full = [&](int s) { return bars + 8u * (1 + s); };                 // NST each
+    auto str_empty = [&](int s) { return bars + 8u * (1 + NST + s); };
+    auto vec_full = [&](int s) { return bars + 8u * (1 + 2 * NST + s); };
+    auto sc_full = [&](int s) { return bars + 8u * (1 + 3 * NST + s); };         // 2 each
+    auto out_full = [&](int s) { return bars + 8u * (3 + 3 * NST + s); };
+    const uint32_t acc_done = bars + 8u * (5 + 3 * NST);
+    const uint32_t tmem_slot = bars + 8u * (6 + 3 * NST);
+    static_assert(8 * (7 + 3 * NST) <= 256, "barrier block");
     uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
-    float* s_vec = reinterpret_cast<float*>(gen + (bars + 256 - base));   // [2 stages][lse2(64) | delta(64)]
+    float* s_vec = reinterpret_cast<float*>(gen + (bars + 256 - base));   // [NST stages][lse2(64) | delta(64)]
     if (base - ptx::smem_u32(smem_raw) > 768u) __trap();
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
@@ -439,11 +442,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
     }
     if (warp == 1 && lane == 0) {
         ptx::mbar_init(stat_full, 1);
-        for (int s = 0; s < NST; ++s) { ptx::mbar_init(str_full(s), 1); ptx::mbar_init(str_empty(s), 1); }
+        for (int s = 0; s < NST; ++s) {
+            ptx::mbar_init(str_full(s), 1); ptx::mbar_init(str_empty(s), 1); ptx::mbar_init(vec_full(s), 1);
+        }
         for (int s = 0; s < 2; ++s) {
-            ptx::mbar_init(sc_full(s), 1);   ptx::mbar_init(sc_empty(s), BWD_EW_WARPS);
-            ptx::mbar_init(out_full(s), BWD_EW_WARPS);  ptx::mbar_init(out_empty(s), 1);
-            ptx::mbar_init(vec_full(s), 1);
+            ptx::mbar_init(sc_full(s), 1);
+            ptx::mbar_init(out_full(s), BWD_EW_WARPS / 2);
         }
         ptx::mbar_init(acc_done, 1);
         ptx::fence_mbar_init();
@@ -459,45 +463,43 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
     const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base)), 0);
 
     if (warp == 0) {
-        // ------------------------------------------------------------------ TMA producer (lane 0) + statistics staging
+        // ------------------------------------------------------------------ TMA producer (one elected lane per wrapper) + statistics staging
         if (niter > 0) {
-            if (lane == 0) {
-                ptx::mbar_arrive_expect_tx(stat_full, 2 * C::STAT);
+            {
+                ptx::mbar_arrive_expect_tx_w(stat_full, 2 * C::STAT);
 #pragma unroll
                 for (int c = 0; c < C::NSUB; ++c) {
                     if (DKV) {
-                        ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, d_model + h * HD + c * 64, r0, b);        // K
-                        ptx::tma_load_3d(sA1 + c * SUB, &tm128, stat_full, 2 * d_model + h * HD + c * 64, r0, b);    // V
+                        ptx::tma_load_3d_w(sA0 + c * SUB, &tm128, stat_full, d_model + h * HD + c * 64, r0, b);        // K
+                        ptx::tma_load_3d_w(sA1 + c * SUB, &tm128, stat_full, 2 * d_model + h * HD + c * 64, r0, b);    // V
                     } else {
-                        ptx::tma_load_3d(sA0 + c * SUB, &tm128, stat_full, h * HD + c * 64, r0, b);                  // Q
-                        ptx::tma_load_3d(sA1 + c * SUB, &tdo128, stat_full, h * HD + c * 64, r0, b);                 // dO
+                        ptx::tma_load_3d_w(sA0 + c * SUB, &tm128, stat_full, h * HD + c * 64, r0, b);                  // Q
+                        ptx::tma_load_3d_w(sA1 + c * SUB, &tdo128, stat_full, h * HD + c * 64, r0, b);                 // dO
                     }
                 }
             }
             for (int n = 0; n < niter; ++n) {
                 const int st = n % NST;
                 const int row0 = (it0 + n) * 64;
-                if (lane == 0) {
+                {
                     ptx::mbar_wait(str_empty(st), ((n / NST) & 1) ^ 1);
                     TRACE(0, n, 0);
-                    ptx::mbar_arrive_expect_tx(str_full(st), 2 * C::STR);
+                    ptx::mbar_arrive_expect_tx_w(str_full(st), 2 * C::STR);
 #pragma unroll
                     for (int c = 0; c < C::NSUB; ++c) {
                         if (DKV) {
-                            ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), h * HD + c * 64, row0, b);    // Q_i
-                            ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tdo64, str_full(st), h * HD + c * 64, row0, b);   // dO_i
+                            ptx::tma_load_3d_w(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), h * HD + c * 64, row0, b);    // Q_i
+                            ptx::tma_load_3d_w(sB1 + st * C::STR + c * SUB64, &tdo64, str_full(st), h * HD + c * 64, row0, b);   // dO_i
                         } else {
-                            ptx::tma_load_3d(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), d_model + h * HD + c * 64, row0, b);      // K_j
-                            ptx::tma_load_3d(sB1 + st * C::STR + c * SUB64, &tm64, str_full(st), 2 * d_model + h * HD + c * 64, row0, b);  // V_j
+                            ptx::tma_load_3d_w(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), d_model + h * HD + c * 64, row0, b);      // K_j
+                            ptx::tma_load_3d_w(sB1 + st * C::STR + c * SUB64, &tm64, str_full(st), 2 * d_model + h * HD + c * 64, row0, b);  // V_j
                         }
                     }
                 }
                 if (DKV) {
-                    // per-column (query) statistics of streamed tile n -> smem stage n&1.  The stage is free once
-                    // every elementwise warp has finished tile n-2, which is what out_full(n-2) says.
-                    const int s = n & 1;
-                    __syncwarp();
-                    if (n >= 2) ptx::mbar_wait(out_full(s), ((n - 2) >> 1) & 1);
+                    // per-column (query) statistics of streamed tile n -> the same ring slot as the tile itself
+                    // (str_empty(st), waited on above, also says the elementwise warps are done with the slot)
+                    const int s = st;
                     float* v = s_vec + s * 128;
                     const int q0 = row0 + lane, q1 = row0 + 32 + lane;
                     v[lane] = q0 < T ? lse_g[q0] * 1.4426950408889634f : INFINITY;
@@ -515,29 +517,27 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
         // elected lane issues inside each wrapper.
         if (niter > 0) {
             constexpr uint32_t id_sc = ptx::umma_idesc_bf16(128, 64, 0, 0);     // scores: both operands K-major
-            constexpr uint32_t id_acc = ptx::umma_idesc_bf16(128, HD, 0, 1);    // accumulate: A K-major (smem out tile), B MN-major
+            constexpr uint32_t id_acc = ptx::umma_idesc_bf16(128, HD, 0, 1);    // accumulate: A from TMEM (K-major), B MN-major
             auto accumulate = [&](int m) {
                 const int sm = m & 1, stm = m % NST;
-                const uint32_t b0 = sB0 + stm * C::STR, b1 = sB1 + stm * C::STR, so = sOut + sm * C::OUT;
+                const uint32_t b0 = sB0 + stm * C::STR, b1 = sB1 + stm * C::STR;
+                const uint32_t ta = tmem + sm * 128;             // bf16 P^T at +16*kk, dS^T (dS) at +64+16*kk
                 ptx::mbar_wait(out_full(sm), (m >> 1) & 1);
                 ptx::tc_fence_after();
                 TRACE(1, m, 3);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {                 // contraction over the 64 streamed rows
+                for (int kk = 0; kk < 4; ++kk) {                 // contraction over the 64 streamed rows, 16 per MMA
                     const uint32_t acc = (m > 0 || kk > 0) ? 1u : 0u;
                     if (DKV) {
-                        // dV += P^T dO_i ; dK += dS^T Q_i
-                        ptx::mma_bf16_ss_w(tmem + C::ACC, ptx::umma_desc(so + kk * 32, 16, 1024),
-                                         ptx::umma_desc(b1 + kk * 2048, SUB64, 1024), id_acc, acc);
-                        ptx::mma_bf16_ss_w(tmem + C::ACC + HD, ptx::umma_desc(so + SUB + kk * 32, 16, 1024),
-                                         ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
+                        // dV += P^T dO_i ; dK += dS^T Q_i      (A from TMEM, B = streamed tile read MN-major)
+                        ptx::mma_bf16_ts_w(tmem + C::ACC, ta + 16 * kk, ptx::umma_desc(b1 + kk * 2048, SUB64, 1024), id_acc, acc);
+                        ptx::mma_bf16_ts_w(tmem + C::ACC + HD, ta + 64 + 16 * kk, ptx::umma_desc(b0 + kk * 2048, SUB64, 1024),
+                                           id_acc, acc);
                     } else {
                         // dQ += dS K_j
-                        ptx::mma_bf16_ss_w(tmem + C::ACC, ptx::umma_desc(so + kk * 32, 16, 1024),
-                                         ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
+                        ptx::mma_bf16_ts_w(tmem + C::ACC, ta + 64 + 16 * kk, ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
                     }
                 }
-                ptx::mma_commit_w(out_empty(sm));
                 ptx::mma_commit_w(str_empty(stm));
                 TRACE(1, m, 4);
             };
@@ -548,7 +548,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
                 const uint32_t b0 = sB0 + st * C::STR, b1 = sB1 + st * C::STR;
                 ptx::mbar_wait(str_full(st), (n / NST) & 1);
                 TRACE(1, n, 0);
-                ptx::mbar_wait(sc_empty(s), ((n >> 1) & 1) ^ 1);
+                // scores stage s is free: its last readers were the accumulate MMAs of tile n-2, issued earlier by
+                // this same warp, and tcgen05.mma executes in issue order
                 ptx::tc_fence_after();
                 TRACE(1, n, 1);
 #pragma unroll
@@ -576,29 +577,30 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
         // NPART warps share each TMEM lane quarter (tcgen05.ld reaches lanes 32*(warp%4)..+31): thread = stationary
         // row, `part` = which slice of the 64 score columns.  The backward needs no row reductions (lse and delta
         // are inputs), so the column split is free; 4 warps per scheduler hide the exp2 / LDS latencies.
-        constexpr int NPART = BWD_EW_WARPS / 4, CPW = 64 / NPART;   // column parts per lane quarter, columns per warp
+        // The 16 warps form two groups of 8 that take alternate tiles (group g owns score stage g), so the exp2-heavy
+        // middle of one tile overlaps the TMEM loads / stores / barrier hand-offs of the next one.
+        constexpr int NPART = BWD_EW_WARPS / 8, CPW = 64 / NPART;   // column parts per lane quarter within a group, columns per warp
         const int q = warp & 3;
-        const int part = (warp - 2) >> 2;
+        const int grp = (warp - 2) >> 3;
+        const int part = ((warp - 2) >> 2) & 1;
         const int row = q * 32 + lane;
         const int srow = r0 + row;                                  // key row (DKV) / query row (DQ)
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
         float my_l2 = INFINITY, my_dl = 0.f;
         if (!DKV && srow < T) { my_l2 = lse_g[srow] * 1.4426950408889634f; my_dl = del_g[srow]; }
-        for (int n = 0; n < niter; ++n) {
+        for (int n = grp; n < niter; n += 2) {
             const int s = n & 1, ph = (n >> 1) & 1;
             const int c0 = (it0 + n) * 64;                          // first streamed row = first score column
-            const float* vl = s_vec + s * 128;
+            const float* vl = s_vec + (n % NST) * 128;
             // causal mask is needed only where the streamed tile overlaps the diagonal
             const bool need_mask = DKV ? (c0 < r0 + 128) : (c0 + 63 > r0);
             if (warp == 2 && lane == 0) TRACE(2, n, 0);
-            if (DKV) ptx::mbar_wait(vec_full(s), ph);
+            if (DKV) ptx::mbar_wait(vec_full(n % NST), (n / NST) & 1);
             if (warp == 2 && lane == 0) TRACE(2, n, 1);
             ptx::mbar_wait(sc_full(s), ph);
             ptx::tc_fence_after();
             if (warp == 2 && lane == 0) TRACE(2, n, 2);
-            ptx::mbar_wait(out_empty(s), ph ^ 1);
             if (warp == 2 && lane == 0) TRACE(2, n, 3);
-            const uint32_t dst = sOut + s * C::OUT + row * 128;
             // MASKED is a compile-time flag so the 7-of-9 off-diagonal tiles carry no compare/select instructions
             auto tile = [&](auto masked_tag) {
                 constexpr bool MASKED = decltype(masked_tag)::value;
@@ -609,12 +611,6 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
                     ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + cb, rs);
                     ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + 64 + cb, rp);
                     ptx::tmem_ld_wait();
-                    if (c == CPW / 16 - 1) {
-                        // this warp's share of both score tiles is in registers: the MMA warp may overwrite it
-                        ptx::tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) ptx::mbar_arrive(sc_empty(s));
-                    }
                     uint32_t pk[8], dk[8];
 #pragma unroll
                     for (int e = 0; e < 16; e += 2) {
@@ -638,24 +634,16 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
                         if (DKV) pk[e >> 1] = pack_bf16x2(p0, p1);
                         dk[e >> 1] = pack_bf16x2(s0, s1);
                     }
-#pragma unroll
-                    for (int ch = 0; ch < 2; ++ch) {
-                        const uint32_t sw = (((uint32_t)(cb / 8 + ch)) ^ ((uint32_t)row & 7u)) << 4;
-                        if (DKV) {
-                            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]),
-                                         "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3]) : "memory");
-                            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + SUB + sw), "r"(dk[4 * ch]),
-                                         "r"(dk[4 * ch + 1]), "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
-                        } else {
-                            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + sw), "r"(dk[4 * ch]), "r"(dk[4 * ch + 1]),
-                                         "r"(dk[4 * ch + 2]), "r"(dk[4 * ch + 3]) : "memory");
-                        }
-                    }
+                    // bf16 results go back into the first 8 of the 16 TMEM columns this warp just read: they are the
+                    // K=16 slice number cb/16 of the A operand of the accumulate MMAs (2 bf16 per 32-bit column)
+                    if (DKV) ptx::tmem_st_32x8(tmem + lane_off + s * 128 + cb, pk);
+                    ptx::tmem_st_32x8(tmem + lane_off + s * 128 + 64 + cb, dk);
                 }
             };
             if (need_mask) tile(MaskOn{}); else tile(MaskOff{});
             if (warp == 2 && lane == 0) TRACE(2, n, 4);
-            ptx::fence_proxy_async_smem();
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(out_full(s));
             if (warp == 2 && lane == 0) TRACE(2, n, 5);
@@ -669,7 +657,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
         bf16* g1 = dqkv + ((size_t)b * T + srow) * (3 * d_model) + h * HD + d_model;                    // dK
         const float f0 = DKV ? 1.f : scale;
 #pragma unroll 1
-        for (int c = part; c < HD / 16; c += NPART) {
+        for (int c = part + 2 * grp; c < HD / 16; c += 2 * NPART) {
             uint32_t r0v[16], r1v[16];
             if (niter > 0) {
                 ptx::tmem_ld_32x16(tmem + lane_off + C::ACC + c * 16, r0v);
@@ -730,8 +718,9 @@ int launch_bwd(const void* qkv, const void* out, const void* dout, const float* 
     if (tma::make_3d(&t64, qkv, 3 * d, T, B, (uint64_t)3 * d * 2, (uint64_t)T * 3 * d * 2, 64, 64, 2)) return -1;
     if (tma::make_3d(&d128, dout, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 128, 2)) return -1;
     if (tma::make_3d(&d64, dout, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 64, 2)) return -1;
-    const int total_warps = B * T * H;
-    B200_CHECK_CUDA(b200_launch(attn_bwd_delta_tc_kernel<HD>, dim3((total_warps + 7) / 8), dim3(256), 0, st, (const bf16*)out, (const bf16*)dout, delta, B, T, H));
+    const long long delta_threads = (long long)B * T * H * (HD / 8);
+    B200_CHECK_CUDA(b200_launch(attn_bwd_delta_tc_kernel<HD>, dim3((unsigned)((delta_threads + 255) / 256)), dim3(256), 0, st,
+                                (const bf16*)out, (const bf16*)dout, delta, B, T, H));
     if (launch_bwd_pass<HD, true>(t128, t64, d128, d64, lse, delta, dqkv, B, T, H, scale, st)) return -1;
     if (launch_bwd_pass<HD, false>(t128, t64, d128, d64, lse, delta, dqkv, B, T, H, scale, st)) return -1;
     return 0;

@@ -93,7 +93,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        // whole warp converged; one elected lane executes each wrapper (uniform operands, see ptx.cuh)
+        {
             int stage = 0;
             uint32_t phase = 0;
             for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
@@ -103,22 +104,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(empty_bar(stage), phase ^ 1);
-                    ptx::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+                    ptx::mbar_arrive_expect_tx_w(full_bar(stage), C::STAGE_BYTES);
                     const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
                     const uint32_t sb = sa + A_BYTES;
                     if (!A_MN) {
-                        ptx::tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, m0);
+                        ptx::tma_load_2d_w(sa, &tmA, full_bar(stage), kb * BK, m0);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BM / 64; ++j)
-                            ptx::tma_load_2d(sa + j * 8192, &tmA, full_bar(stage), m0 + j * 64, kb * BK);
+                            ptx::tma_load_2d_w(sa + j * 8192, &tmA, full_bar(stage), m0 + j * 64, kb * BK);
                     }
                     if (!B_MN) {
-                        ptx::tma_load_2d(sb, &tmB, full_bar(stage), kb * BK, n0);
+                        ptx::tma_load_2d_w(sb, &tmB, full_bar(stage), kb * BK, n0);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
-                            ptx::tma_load_2d(sb + j * 8192, &tmB, full_bar(stage), n0 + j * 64, kb * BK);
+                            ptx::tma_load_2d_w(sb + j * 8192, &tmB, full_bar(stage), n0 + j * 64, kb * BK);
                     }
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }

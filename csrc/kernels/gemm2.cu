@@ -99,11 +99,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer (both CTAs)
-        if (lane == 0) {
+        // whole warp converged; one elected lane executes each wrapper (uniform operands, see ptx.cuh)
+        {
             int stage = 0;
             uint32_t phase = 0;
             unsigned ready_mask = 0;                    // chunks already seen valid (AG)
-            const int ag_epoch = (AG && ag.flags != nullptr) ? *ag.epoch : 0;
+            const int ag_epoch = (AG && ag.flags != nullptr) ? __shfl_sync(0xffffffffu, *ag.epoch, 0) : 0;
             for (int u = pair; u < nunits; u += npairs) {
                 const int tile = u % ntiles, split = u / ntiles;
                 const int m0 = (tile % p.num_m) * 256 + (int)rank * 128;
@@ -118,7 +119,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         const int c0 = (int)((e0 - ag.layer_start) / ag.chunk), c1 = (int)((e1 - 1 - ag.layer_start) / ag.chunk);
                         for (int c = c0; c <= c1; ++c) {
                             if (c == ag.rank || (ready_mask >> c) & 1u) continue;
-                            while (ld_acquire_gpu(ag.flags + c) < ag_epoch) __nanosleep(32);
+                            while (__shfl_sync(0xffffffffu, ld_acquire_gpu(ag.flags + c), 0) < ag_epoch) __nanosleep(32);
                             ready_mask |= 1u << c;
                         }
                         asm volatile("fence.proxy.async;" ::: "memory");   // gathered by generic stores, read by TMA
@@ -126,22 +127,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 }
                 for (int kb = kb0; kb < kb1; ++kb) {
                     ptx::mbar_wait(empty_bar(stage), phase ^ 1);
-                    if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+                    if (rank == 0) ptx::mbar_arrive_expect_tx_w(full_bar(stage), 2 * C::STAGE_BYTES);
                     const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
                     const uint32_t sb = sa + A_BYTES;
                     if (!A_MN) {
-                        ptx::tma_load_2d_2sm(sa, &tmA, full_bar(stage), kb * BK, m0);
+                        ptx::tma_load_2d_2sm_w(sa, &tmA, full_bar(stage), kb * BK, m0);
                     } else {
 #pragma unroll
                         for (int j = 0; j < 2; ++j)
-                            ptx::tma_load_2d_2sm(sa + j * 8192, &tmA, full_bar(stage), m0 + j * 64, kb * BK);
+                            ptx::tma_load_2d_2sm_w(sa + j * 8192, &tmA, full_bar(stage), m0 + j * 64, kb * BK);
                     }
                     if (!B_MN) {
-                        ptx::tma_load_2d_2sm(sb, &tmB, full_bar(stage), kb * BK, n0);
+                        ptx::tma_load_2d_2sm_w(sb, &tmB, full_bar(stage), kb * BK, n0);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BN / 128; ++j)
-                            ptx::tma_load_2d_2sm(sb + j * 8192, &tmB, full_bar(stage), n0 + j * 64, kb * BK);
+                            ptx::tma_load_2d_2sm_w(sb + j * 8192, &tmB, full_bar(stage), n0 + j * 64, kb * BK);
                     }
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }

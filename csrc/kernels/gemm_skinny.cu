@@ -78,15 +78,16 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)), 0);
 
     if (warp == 0) {
-        if (lane == 0) {
+        // whole warp converged; one elected lane executes each wrapper (uniform operands, see ptx.cuh)
+        {
             int stage = 0;
             uint32_t phase = 0;
             for (int kb = kb0; kb < kb1; ++kb) {
                 ptx::mbar_wait(empty_bar(stage), phase ^ 1);
-                ptx::mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+                ptx::mbar_arrive_expect_tx_w(full_bar(stage), C::STAGE_BYTES);
                 const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
-                ptx::tma_load_2d(sa, &tmW, full_bar(stage), kb * BK, n0);            // 128 weight rows
-                ptx::tma_load_2d(sa + A_BYTES, &tmX, full_bar(stage), kb * BK, 0);   // the whole (padded) batch
+                ptx::tma_load_2d_w(sa, &tmW, full_bar(stage), kb * BK, n0);            // 128 weight rows
+                ptx::tma_load_2d_w(sa + A_BYTES, &tmX, full_bar(stage), kb * BK, 0);   // the whole (padded) batch
                 if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
             }
         }
