@@ -37,31 +37,29 @@ template <int HD> struct ACfg {
     static constexpr int S_BUFS = HD == 64 ? 1 : 2;
     static constexpr int TMEM_COLS = HD == 64 ? 256 : 512;
     static constexpr int O_COL = 128 * S_BUFS;
-    // smem: Q | K[2] | V[2] | P (2 sub-tiles) | barriers
+    // smem: Q | K[2] | V[2] | barriers
     // + barriers (256 B) + alignment slack (768 B: lets two hs=64 CTAs share one SM's 227 KB)
-    static constexpr int USED = TILE + 2 * TILE + 2 * TILE + 2 * SUB + 256;
+    static constexpr int USED = TILE + 2 * TILE + 2 * TILE + 256;
     static constexpr int SMEM = USED + 768;
 };
 
 template <int HD>
 __global__ void __launch_bounds__(NTHREADS, HD == 64 ? 2 : 1)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
-                   float* __restrict__ lse_out, int T, int H, float scale_log2) {
+                   float* __restrict__ lse_out, int T, int H, int HB, int nqt, float scale_log2) {
     using C = ACfg<HD>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t sQ = base;
     const uint32_t sK = sQ + C::TILE;
     const uint32_t sV = sK + 2 * C::TILE;
-    const uint32_t sP = sV + 2 * C::TILE;
-    const uint32_t bars = sP + 2 * SUB;
+    const uint32_t bars = sV + 2 * C::TILE;
     const uint32_t q_full = bars;
     auto k_full = [&](int s) { return bars + 8u * (1 + s); };
     auto k_empty = [&](int s) { return bars + 8u * (3 + s); };
     auto v_full = [&](int s) { return bars + 8u * (5 + s); };
     auto v_empty = [&](int s) { return bars + 8u * (7 + s); };
     auto s_full = [&](int s) { return bars + 8u * (9 + s); };
-    auto s_empty = [&](int s) { return bars + 8u * (11 + s); };
     const uint32_t p_full = bars + 8u * 13;
     const uint32_t pv_done = bars + 8u * 14;
     const uint32_t tmem_slot = bars + 8u * 15;
@@ -69,8 +67,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     if (base - ptx::smem_u32(smem_raw) > 768u) __trap();   // dynamic smem window less aligned than assumed
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
-    const int qt = gridDim.x - 1 - blockIdx.x;     // heavy (late) query tiles first
-    const int h = blockIdx.y, b = blockIdx.z;
+    // 1-D grid in longest-processing-time order: ALL (b, h) of the heaviest (last) query tile first
+    const int rank = (int)blockIdx.x / HB, hb = (int)blockIdx.x - rank * HB;
+    const int qt = nqt - 1 - rank;
+    const int h = hb % H, b = hb / H;
     const int q0 = qt * BM;
     const int d_model = H * HD;
     const int ntiles = qt + 1;                     // causal: key tiles 0..qt
@@ -84,7 +84,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(k_full(s), 1); ptx::mbar_init(k_empty(s), 1);
             ptx::mbar_init(v_full(s), 1); ptx::mbar_init(v_empty(s), 1);
-            ptx::mbar_init(s_full(s), 1); ptx::mbar_init(s_empty(s), 4);
+            ptx::mbar_init(s_full(s), 1);
         }
         ptx::mbar_init(p_full, 4);
         ptx::mbar_init(pv_done, 1);
@@ -128,10 +128,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         {
             constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(128, 128, 0, 0);
             constexpr uint32_t idesc_pv = ptx::umma_idesc_bf16(128, HD, 0, 1);
+            // S buffer sb is rewritten by S_{j} only after PV_{j - S_BUFS} (which read the bf16 P aliased onto it) was
+            // issued by this same warp: tcgen05.mma executes in issue order, so no barrier is needed for that.
             auto issue_s = [&](int j) {
                 const int st = j & 1, sb = j % C::S_BUFS;
                 ptx::mbar_wait(k_full(st), (j >> 1) & 1);
-                ptx::mbar_wait(s_empty(sb), ((j / C::S_BUFS) & 1) ^ 1);
                 ptx::tc_fence_after();
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk) {
@@ -145,20 +146,20 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             ptx::mbar_wait(q_full, 0);
             issue_s(0);
             for (int j = 0; j < ntiles; ++j) {
-                const int st = j & 1;
-                if (j + 1 < ntiles) issue_s(j + 1);
+                const int st = j & 1, sb = j % C::S_BUFS;
+                if (C::S_BUFS == 2 && j + 1 < ntiles) issue_s(j + 1);      // other buffer: overlaps softmax_j
                 ptx::mbar_wait(p_full, j & 1);
                 ptx::mbar_wait(v_full(st), (j >> 1) & 1);
                 ptx::tc_fence_after();
 #pragma unroll
                 for (int kk = 0; kk < BN / 16; ++kk) {
-                    // A = P [128 q x 128 kv], K-major, two 64-wide sub-tiles; B = V [kv x hs], MN-major
-                    const uint64_t ad = ptx::umma_desc(sP + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
+                    // A = P [128 q x 128 kv] bf16 in TMEM (8 columns per K=16 slice, aliased onto S); B = V [kv x hs], MN-major
                     const uint64_t bd = ptx::umma_desc(sV + st * C::TILE + kk * 2048, SUB, 1024);
-                    ptx::mma_bf16_ss_w(tmem + C::O_COL, ad, bd, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                    ptx::mma_bf16_ts_w(tmem + C::O_COL, tmem + sb * 128 + 8 * kk, bd, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
                 }
                 ptx::mma_commit_w(pv_done);
                 ptx::mma_commit_w(v_empty(st));
+                if (C::S_BUFS == 1 && j + 1 < ntiles) issue_s(j + 1);      // same buffer: in order behind PV_j
             }
         }
     } else {
@@ -175,80 +176,65 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             const uint32_t ts = tmem + lane_off + sb * 128;
             const bool diag = (j == qt);
             const int k0 = j * BN;
-            // ---- pass 1: row maximum
-            float mx = -INFINITY;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                uint32_t r[32];
-                ptx::tmem_ld_32x32(ts + c * 32, r);
-                ptx::tmem_ld_wait();
+            // ---- the whole score row (128 fp32) is read from TMEM ONCE and kept in registers
+            uint32_t r[4][32];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    float v = __uint_as_float(r[i]);
-                    if (diag && (k0 + c * 32 + i > qrow)) v = -INFINITY;
-                    mx = fmaxf(mx, v);
-                }
+            for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32(ts + c * 32, r[c]);
+            ptx::tmem_ld_wait();
+            float mx = -INFINITY;
+            if (diag) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (k0 + c * 32 + i > qrow) r[c][i] = 0xff800000u;      // -inf: exp2 gives exactly 0
             }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[c][i]));
             const float xmax = mx * scale_log2;
             const bool need = xmax > m_used + 8.f;          // also true on the first tile (m_used = -inf)
             const float m_new = need ? xmax : m_used;
             const float alpha = need ? exp2f(m_used - m_new) : 1.f;
-            // O and the P buffer belong to PV_{j-1} until it has completed
+            // O belongs to PV_{j-1} until it has completed
             if (j > 0) {
                 ptx::mbar_wait(pv_done, (j - 1) & 1);
                 ptx::tc_fence_after();
                 if (__any_sync(0xffffffffu, need)) {
 #pragma unroll 1
                     for (int c = 0; c < HD / 32; ++c) {
-                        uint32_t r[32];
-                        ptx::tmem_ld_32x32(tmem + lane_off + C::O_COL + c * 32, r);
+                        uint32_t o[32];
+                        ptx::tmem_ld_32x32(tmem + lane_off + C::O_COL + c * 32, o);
                         ptx::tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-                        ptx::tmem_st_32x32(tmem + lane_off + C::O_COL + c * 32, r);
+                        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        ptx::tmem_st_32x32(tmem + lane_off + C::O_COL + c * 32, o);
                     }
-                    ptx::tmem_st_wait();
                 }
             }
             l *= alpha;
             m_used = m_new;
-            // ---- pass 2: probabilities -> bf16 -> swizzled smem (K-major A operand of the PV MMA)
-            float rs = 0.f;
-#pragma unroll 1
+            // ---- probabilities -> bf16 pairs -> back into the first 64 columns of the S buffer (A operand of PV)
+            float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
             for (int c = 0; c < 4; ++c) {
-                uint32_t r[32];
-                ptx::tmem_ld_32x32(ts + c * 32, r);
-                ptx::tmem_ld_wait();
                 uint32_t pk[16];
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
-                    float p0 = exp2f(__uint_as_float(r[i]) * scale_log2 - m_used);
-                    float p1 = exp2f(__uint_as_float(r[i + 1]) * scale_log2 - m_used);
-                    if (diag) {
-                        if (k0 + c * 32 + i > qrow) p0 = 0.f;
-                        if (k0 + c * 32 + i + 1 > qrow) p1 = 0.f;
-                    }
-                    rs += p0 + p1;
+                    const float p0 = exp2f(__uint_as_float(r[c][i]) * scale_log2 - m_used);
+                    const float p1 = exp2f(__uint_as_float(r[c][i + 1]) * scale_log2 - m_used);
+                    rs0 += p0;
+                    rs1 += p1;
                     pk[i >> 1] = pack_bf16x2(p0, p1);
                 }
-                // 32 columns = 4 chunks of 16 B; column block c -> sub-tile c/2, chunks (c%2)*4 .. +3
-                const uint32_t dst = sP + (c >> 1) * SUB + row * 128;
-#pragma unroll
-                for (int ch = 0; ch < 4; ++ch) {
-                    const uint32_t chunk = (uint32_t)((c & 1) * 4 + ch);
-                    const uint32_t addr = dst + ((chunk ^ ((uint32_t)row & 7u)) << 4);
-                    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]),
-                                 "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3]) : "memory");
-                }
+                ptx::tmem_st_32x16(ts + c * 16, pk);
             }
-            l += rs;
+            l += rs0 + rs1;
+            ptx::tmem_st_wait();
             ptx::tc_fence_before();
-            ptx::fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) {
-                ptx::mbar_arrive(p_full);
-                ptx::mbar_arrive(s_empty(sb));
-            }
+            if (lane == 0) ptx::mbar_arrive(p_full);
         }
         // ---- epilogue: O / l -> bf16 -> smem (Q's tile is free now) -> TMA store; LSE -> global
         ptx::mbar_wait(pv_done, (ntiles - 1) & 1);
@@ -304,8 +290,9 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, floa
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
         cfg = true;
     }
-    dim3 grid((T + BM - 1) / BM, H, B);
-    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NTHREADS), C::SMEM, st, tq, to, lse, T, H, scale * 1.4426950408889634f));
+    const int nqt = (T + BM - 1) / BM;
+    B200_CHECK_CUDA(b200_launch(kern, dim3(nqt * H * B), dim3(NTHREADS), C::SMEM, st, tq, to, lse, T, H, H * B, nqt,
+                                scale * 1.4426950408889634f));
     return 0;
 }
 
