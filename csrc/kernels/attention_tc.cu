@@ -298,37 +298,43 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, floa
 
 
 // =============================================================================================
-// Backward on tcgen05: two passes of ONE kernel template, no atomics, no fp32 scratch.
+// Backward on tcgen05: two passes of ONE persistent kernel template, no atomics, no fp32 scratch.
 //
-//   pass DKV (key-stationary):   CTA = 128 keys of one (b, h); streams 64-query tiles i >= diagonal
+//   pass DKV (key-stationary):   work item = 128 keys of one (b, h); streams 64-query tiles i >= diagonal
 //        S^T = K Q_i^T , dP^T = V dO_i^T                    2 MMAs (M=128 keys, N=64 queries) -> TMEM
-//        P^T = exp2(S^T c - lse[q]) , dS^T = P^T (dP^T - delta[q]) scale      thread = key row
+//        P^T = exp2(S^T c - lse[q]) , dS^T = P^T (dP^T - delta[q])            thread = key row
 //        dV += P^T dO_i , dK += dS^T Q_i                    2 MMAs accumulate in TMEM over all i
-//   pass DQ (query-stationary):  CTA = 128 queries; streams 64-key tiles j <= diagonal
+//   pass DQ (query-stationary):  work item = 128 queries; streams 64-key tiles j <= diagonal
 //        S = Q K_j^T , dP = dO V_j^T                        2 MMAs (M=128 queries, N=64 keys)
-//        dS = P (dP - delta[q]) scale                       thread = query row
+//        dS = P (dP - delta[q])                             thread = query row
 //        dQ += dS K_j                                       1 MMA accumulates in TMEM over all j
+//   (the 1/sqrt(hs) factor of dS is applied once per output element in the epilogue)
 //
-// Both passes have the same shape: two "score" MMAs [128 x 64] with K = hs from K-major smem tiles,
-// an elementwise stage that writes bf16 tiles [128 x 64] to swizzled smem, and "accumulate" MMAs
-// [128 x hs] with K = 64 whose B operand is the streamed tile read MN-major.  Recomputing S in the
-// second pass costs 2 extra MMAs per tile pair but removes the cross-CTA dQ reduction entirely
-// (fp32 RED traffic + a conversion pass were the bottleneck of the single-pass version).
-// One CTA per SM, software-pipelined INSIDE the CTA: the score accumulators (TMEM) and the bf16 out tiles (smem)
-// are double-buffered, so while the elementwise warps work on tile n the tensor pipe runs the accumulate MMAs
-// of tile n-1 and the score MMAs of tile n+1 (issue order: scores(n+1), then acc(n) once the out tile is
-// written).  Streamed tiles are triple-buffered.  The first version ran two independent CTAs per SM instead
-// and left the tensor pipe 20% busy: every CTA spent most of its time in the serial chain MMA -> commit ->
-// wake-up -> exp -> arrive -> wake-up -> MMA (ncu: elementwise warps waiting on sc_full).
-// CTAs are ordered heaviest stationary tile first (longest-processing-time order) so the causal triangle
-// does not leave a long tail.
-// Warp roles: 0 TMA (+ per-tile lse/delta staging in the key-stationary pass), 1 MMA, 2-17 elementwise +
-// epilogue; four elementwise warps share each TMEM lane quarter and split the 64 score columns.
+// Both passes have the same shape: two "score" MMAs [128 x 64] with K = hs from K-major smem tiles, an elementwise
+// stage, and "accumulate" MMAs [128 x hs] with K = 64 whose A operand is the bf16 result of the elementwise stage
+// read straight from TENSOR MEMORY (it is written back over the fp32 scores it came from, 2 bf16 per column) and
+// whose B operand is the streamed smem tile read MN-major.  Recomputing S in the second pass costs 2 extra MMAs per
+// tile pair but removes the cross-CTA dQ reduction entirely (fp32 RED traffic + a conversion pass were the
+// bottleneck of a single-pass version).
+//
+// Pipeline (what the in-kernel timeline, tools/attn_trace.cu, and ncu showed along the way):
+//   * one PERSISTENT CTA per SM walks a static list of work items (heaviest stationary tiles first, round-robin
+//     over CTAs): the next item's stationary tiles, its first streamed tiles and its first score MMAs are in flight
+//     while the current item's accumulators are drained, so the ~5000 clk of per-item prologue / cold TMA /
+//     epilogue that a CTA-per-item launch exposed (40% of the pass at T = 1024) are hidden;
+//   * score accumulators are double-buffered in TMEM: the MMA warp issues scores(n+1) BEFORE the accumulate MMAs
+//     of tile n, so the tensor pipe works while the elementwise warps are on tile n;
+//   * 16 elementwise warps in two groups that take alternate tiles (group g owns score buffer g): the exp2-heavy
+//     middle of one tile overlaps the TMEM loads / stores / barrier hand-offs of the next;
+//   * streamed tiles sit in a 6-deep (hs=64) / 4-deep (hs=128) TMA ring: a cold L2 answers in ~2000 clk;
+//   * every tcgen05.mma / TMA is issued with warp-uniform operands by one elected lane (see ptx.cuh): the
+//     single-lane form cost 70-100 clk per MMA, three times the 32 clk a [128x64x16] MMA takes.
+// Warp roles: 0 TMA (+ per-tile lse/delta staging in the key-stationary pass), 1 MMA, 2-17 elementwise + epilogue.
 // =============================================================================================
 constexpr int SUB64 = 64 * 64 * 2;     // [64 rows x 64 cols] bf16 sub-tile = 8 KiB
 
 // Optional in-kernel timeline (tools/attn_trace.cu builds this file with -DATTN_TRACE): CTA 0 records clock64()
-// at its pipeline hand-offs.  Compiled out of the library.
+// at the pipeline hand-offs of its first work item.  Compiled out of the library.
 #ifdef ATTN_TRACE
 __device__ long long g_attn_trace[2][3][64][8];   // [pass][role][tile][event]
 #define TRACE(role, n, k) do { if (blockIdx.x == 0 && (n) < 64) g_attn_trace[DKV ? 1 : 0][role][n][k] = clock64(); } while (0)
@@ -340,14 +346,16 @@ template <int HD, bool DKV> struct BCfg {
     static constexpr int NSUB = HD / 64;
     static constexpr int STAT = NSUB * SUB;                 // stationary tile [128 x HD]
     static constexpr int STR = NSUB * SUB64;                // streamed tile  [64 x HD]
-    static constexpr int NST = HD == 64 ? 6 : 4;            // streamed stages (TMA latency from a cold L2 is ~2000 clk)
-    static constexpr int NACC = DKV ? 2 : 1;                // TMEM accumulators (dV, dK | dQ)
-    static constexpr int ACC = 256;                         // TMEM columns: scores stage s at 128*s (S | dP), then acc
+    static constexpr int NST = HD == 64 ? 6 : 4;            // streamed stages
+    static constexpr int STAT_BUFS = HD == 64 ? 2 : 1;      // stationary operand pairs resident at once
+    static constexpr int NACC = DKV ? 2 : 1;                // accumulators per item (dV, dK | dQ)
+    static constexpr int ACC_BUFS = (256 + 2 * NACC * HD <= 512) ? 2 : 1;
+    static constexpr int ACC = 256;                         // TMEM columns: scores stage s at 128*s (S | dP), then accumulators
     static constexpr int TMEM_COLS = 512;
-    // stat x2 | streamed x2 tensors x NST stages | barriers (256) + lse/delta staging (512 per stage)
-    static constexpr int USED = 2 * STAT + 2 * NST * STR + 256 + NST * 512;
-    static constexpr int SMEM = USED + 768;
-    static_assert(ACC + NACC * HD <= 512, "TMEM budget");
+    // stationary x2 tensors x STAT_BUFS | streamed x2 tensors x NST stages | barriers (256) + lse/delta staging (512 per stage)
+    static constexpr int USED = 2 * STAT * STAT_BUFS + 2 * NST * STR + 256 + NST * 512;
+    static constexpr int SMEM = USED + 1024;
+    static_assert(ACC + ACC_BUFS * NACC * HD <= 512, "TMEM budget");
     static_assert(SMEM <= 232448, "smem budget");
 };
 
@@ -380,7 +388,7 @@ __global__ void __launch_bounds__(256) attn_bwd_delta_tc_kernel(const bf16* __re
 }
 
 // tm128 / tm64: qkv viewed [B][T][3d] with 128- / 64-row boxes; tdo128 / tdo64: dO viewed [B][T][d].
-// Grid: 1-D, ntile * H * B CTAs; blockIdx.x / (H*B) is the stationary tile's rank by amount of work.
+// Work item i (0 = heaviest): stationary tile rank i / HB of (b, h) = i % HB; CTA c takes items c, c + grid, ...
 template <int HD, bool DKV>
 __global__ void __launch_bounds__(NTHREADS_BWD, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm64,
@@ -388,55 +396,60 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
                    const float* __restrict__ lse, const float* __restrict__ delta, bf16* __restrict__ dqkv, int T, int H,
                    int HB, int ntile, float scale, float scale_log2) {
     using C = BCfg<HD, DKV>;
-    constexpr int NST = C::NST;
+    constexpr int NST = C::NST, SB = C::STAT_BUFS, AB = C::ACC_BUFS;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t sA0 = base;                          // stationary operand of score MMA 1 (K | Q)
-    const uint32_t sA1 = sA0 + C::STAT;                 // stationary operand of score MMA 2 (V | dO)
-    const uint32_t sB0 = sA1 + C::STAT;                 // streamed, NST stages: (Q_i | K_j)
+    auto sA0 = [&](int p) { return base + (uint32_t)p * 2 * C::STAT; };             // stationary operand of score MMA 1 (K | Q)
+    auto sA1 = [&](int p) { return base + (uint32_t)p * 2 * C::STAT + C::STAT; };   // stationary operand of score MMA 2 (V | dO)
+    const uint32_t sB0 = base + SB * 2 * C::STAT;       // streamed, NST stages: (Q_i | K_j)
     const uint32_t sB1 = sB0 + NST * C::STR;            // streamed, NST stages: (dO_i | V_j)
     const uint32_t bars = sB1 + NST * C::STR;
-    const uint32_t stat_full = bars;
-    auto str_full = [&](int s) { return bars + 8u * (1 + s); };                 // NST each
-    auto str_empty = [&](int s) { return bars + 8u * (1 + NST + s); };
-    auto vec_full = [&](int s) { return bars + 8u * (1 + 2 * NST + s); };
-    auto sc_full = [&](int s) { return bars + 8u * (1 + 3 * NST + s); };         // 2 each
-    auto out_full = [&](int s) { return bars + 8u * (3 + 3 * NST + s); };
-    const uint32_t acc_done = bars + 8u * (5 + 3 * NST);
-    const uint32_t tmem_slot = bars + 8u * (6 + 3 * NST);
-    static_assert(8 * (7 + 3 * NST) <= 256, "barrier block");
+    auto str_full = [&](int s) { return bars + 8u * s; };                         // NST each
+    auto str_empty = [&](int s) { return bars + 8u * (NST + s); };
+    auto vec_full = [&](int s) { return bars + 8u * (2 * NST + s); };
+    auto sc_full = [&](int s) { return bars + 8u * (3 * NST + s); };              // 2 each
+    auto out_full = [&](int s) { return bars + 8u * (3 * NST + 2 + s); };
+    auto stat_full = [&](int s) { return bars + 8u * (3 * NST + 4 + s); };
+    auto stat_empty = [&](int s) { return bars + 8u * (3 * NST + 6 + s); };
+    auto acc_full = [&](int s) { return bars + 8u * (3 * NST + 8 + s); };
+    auto acc_empty = [&](int s) { return bars + 8u * (3 * NST + 10 + s); };
+    const uint32_t tmem_slot = bars + 8u * (3 * NST + 12);
+    static_assert(8 * (3 * NST + 13) <= 256, "barrier block");
     uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
     float* s_vec = reinterpret_cast<float*>(gen + (bars + 256 - base));   // [NST stages][lse2(64) | delta(64)]
-    if (base - ptx::smem_u32(smem_raw) > 768u) __trap();
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
-    const int rank = (int)blockIdx.x / HB, hb = (int)blockIdx.x - rank * HB;
-    const int h = hb % H, b = hb / H;
     const int d_model = H * HD;
     const int n64 = (T + 63) / 64;
-    // stationary tile index (rank 0 = most streamed tiles) and the range of streamed 64-row tiles
-    const int ts = DKV ? rank : ntile - 1 - rank;
-    const int r0 = ts * 128;                            // first key (DKV) / query (DQ) row of the stationary tile
-    const int it0 = DKV ? 2 * ts : 0;                   // first streamed tile
-    const int it1 = DKV ? n64 : min(n64, 2 * ts + 2);   // one past the last streamed tile
-    const int niter = it1 - it0;
-    const float* lse_g = lse + ((size_t)b * H + h) * T;
-    const float* del_g = delta + ((size_t)b * H + h) * T;
+    const int nitems = ntile * HB;
+
+    // decode of work item `it`: stationary tile, (b, h) and its range of streamed 64-row tiles
+    struct Item { int h, b, r0, it0, niter; };
+    auto decode = [&](int it) {
+        Item w;
+        const int rank = it / HB, hb = it - rank * HB;
+        w.h = hb % H; w.b = hb / H;
+        const int ts = DKV ? rank : ntile - 1 - rank;     // rank 0 = most streamed tiles
+        w.r0 = ts * 128;                                    // first key (DKV) / query (DQ) row of the stationary tile
+        w.it0 = DKV ? 2 * ts : 0;
+        w.niter = (DKV ? n64 : min(n64, 2 * ts + 2)) - w.it0;
+        return w;
+    };
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm128); ptx::prefetch_tmap(&tm64);
         ptx::prefetch_tmap(&tdo128); ptx::prefetch_tmap(&tdo64);
     }
     if (warp == 1 && lane == 0) {
-        ptx::mbar_init(stat_full, 1);
         for (int s = 0; s < NST; ++s) {
             ptx::mbar_init(str_full(s), 1); ptx::mbar_init(str_empty(s), 1); ptx::mbar_init(vec_full(s), 1);
         }
         for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(sc_full(s), 1);
             ptx::mbar_init(out_full(s), BWD_EW_WARPS / 2);
+            ptx::mbar_init(stat_full(s), 1);  ptx::mbar_init(stat_empty(s), 1);
+            ptx::mbar_init(acc_full(s), 1);   ptx::mbar_init(acc_empty(s), BWD_EW_WARPS);
         }
-        ptx::mbar_init(acc_done, 1);
         ptx::fence_mbar_init();
     }
     if (warp == 2) {
@@ -451,225 +464,239 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_const
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer (one elected lane per wrapper) + statistics staging
-        if (niter > 0) {
-            {
-                ptx::mbar_arrive_expect_tx_w(stat_full, 2 * C::STAT);
+        int g = 0;                                           // streamed tiles issued so far (all items)
+        int k = 0;                                           // items started so far
+        for (int it = blockIdx.x; it < nitems; it += gridDim.x, ++k) {
+            const Item w = decode(it);
+            const int sp = k % SB;
+            ptx::mbar_wait(stat_empty(sp), ((k / SB) & 1) ^ 1);
+            ptx::mbar_arrive_expect_tx_w(stat_full(sp), 2 * C::STAT);
+#pragma unroll
+            for (int c = 0; c < C::NSUB; ++c) {
+                if (DKV) {
+                    ptx::tma_load_3d_w(sA0(sp) + c * SUB, &tm128, stat_full(sp), d_model + w.h * HD + c * 64, w.r0, w.b);        // K
+                    ptx::tma_load_3d_w(sA1(sp) + c * SUB, &tm128, stat_full(sp), 2 * d_model + w.h * HD + c * 64, w.r0, w.b);    // V
+                } else {
+                    ptx::tma_load_3d_w(sA0(sp) + c * SUB, &tm128, stat_full(sp), w.h * HD + c * 64, w.r0, w.b);                  // Q
+                    ptx::tma_load_3d_w(sA1(sp) + c * SUB, &tdo128, stat_full(sp), w.h * HD + c * 64, w.r0, w.b);                 // dO
+                }
+            }
+            const float* lse_g = lse + ((size_t)w.b * H + w.h) * T;
+            const float* del_g = delta + ((size_t)w.b * H + w.h) * T;
+            for (int n = 0; n < w.niter; ++n, ++g) {
+                const int st = g % NST;
+                const int row0 = (w.it0 + n) * 64;
+                ptx::mbar_wait(str_empty(st), ((g / NST) & 1) ^ 1);
+                if (k == 0) TRACE(0, n, 0);
+                ptx::mbar_arrive_expect_tx_w(str_full(st), 2 * C::STR);
 #pragma unroll
                 for (int c = 0; c < C::NSUB; ++c) {
                     if (DKV) {
-                        ptx::tma_load_3d_w(sA0 + c * SUB, &tm128, stat_full, d_model + h * HD + c * 64, r0, b);        // K
-                        ptx::tma_load_3d_w(sA1 + c * SUB, &tm128, stat_full, 2 * d_model + h * HD + c * 64, r0, b);    // V
+                        ptx::tma_load_3d_w(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), w.h * HD + c * 64, row0, w.b);    // Q_i
+                        ptx::tma_load_3d_w(sB1 + st * C::STR + c * SUB64, &tdo64, str_full(st), w.h * HD + c * 64, row0, w.b);   // dO_i
                     } else {
-                        ptx::tma_load_3d_w(sA0 + c * SUB, &tm128, stat_full, h * HD + c * 64, r0, b);                  // Q
-                        ptx::tma_load_3d_w(sA1 + c * SUB, &tdo128, stat_full, h * HD + c * 64, r0, b);                 // dO
-                    }
-                }
-            }
-            for (int n = 0; n < niter; ++n) {
-                const int st = n % NST;
-                const int row0 = (it0 + n) * 64;
-                {
-                    ptx::mbar_wait(str_empty(st), ((n / NST) & 1) ^ 1);
-                    TRACE(0, n, 0);
-                    ptx::mbar_arrive_expect_tx_w(str_full(st), 2 * C::STR);
-#pragma unroll
-                    for (int c = 0; c < C::NSUB; ++c) {
-                        if (DKV) {
-                            ptx::tma_load_3d_w(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), h * HD + c * 64, row0, b);    // Q_i
-                            ptx::tma_load_3d_w(sB1 + st * C::STR + c * SUB64, &tdo64, str_full(st), h * HD + c * 64, row0, b);   // dO_i
-                        } else {
-                            ptx::tma_load_3d_w(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), d_model + h * HD + c * 64, row0, b);      // K_j
-                            ptx::tma_load_3d_w(sB1 + st * C::STR + c * SUB64, &tm64, str_full(st), 2 * d_model + h * HD + c * 64, row0, b);  // V_j
-                        }
+                        ptx::tma_load_3d_w(sB0 + st * C::STR + c * SUB64, &tm64, str_full(st), d_model + w.h * HD + c * 64, row0, w.b);      // K_j
+                        ptx::tma_load_3d_w(sB1 + st * C::STR + c * SUB64, &tm64, str_full(st), 2 * d_model + w.h * HD + c * 64, row0, w.b);  // V_j
                     }
                 }
                 if (DKV) {
-                    // per-column (query) statistics of streamed tile n -> the same ring slot as the tile itself
+                    // per-column (query) statistics of this streamed tile -> the same ring slot as the tile itself
                     // (str_empty(st), waited on above, also says the elementwise warps are done with the slot)
-                    const int s = st;
-                    float* v = s_vec + s * 128;
+                    float* v = s_vec + st * 128;
                     const int q0 = row0 + lane, q1 = row0 + 32 + lane;
                     v[lane] = q0 < T ? lse_g[q0] * 1.4426950408889634f : INFINITY;
                     v[32 + lane] = q1 < T ? lse_g[q1] * 1.4426950408889634f : INFINITY;
                     v[64 + lane] = q0 < T ? del_g[q0] : 0.f;
                     v[96 + lane] = q1 < T ? del_g[q1] : 0.f;
                     __syncwarp();
-                    if (lane == 0) { ptx::mbar_arrive(vec_full(s)); TRACE(0, n, 1); }
+                    if (lane == 0) { ptx::mbar_arrive(vec_full(st)); if (k == 0) TRACE(0, n, 1); }
                 }
             }
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        // The whole warp runs this loop converged (uniform operands -> no per-MMA R2UR loops, see ptx.cuh); one
-        // elected lane issues inside each wrapper.
-        if (niter > 0) {
-            constexpr uint32_t id_sc = ptx::umma_idesc_bf16(128, 64, 0, 0);     // scores: both operands K-major
-            constexpr uint32_t id_acc = ptx::umma_idesc_bf16(128, HD, 0, 1);    // accumulate: A from TMEM (K-major), B MN-major
-            auto accumulate = [&](int m) {
-                const int sm = m & 1, stm = m % NST;
-                const uint32_t b0 = sB0 + stm * C::STR, b1 = sB1 + stm * C::STR;
-                const uint32_t ta = tmem + sm * 128;             // bf16 P^T at +16*kk, dS^T (dS) at +64+16*kk
-                ptx::mbar_wait(out_full(sm), (m >> 1) & 1);
-                ptx::tc_fence_after();
-                TRACE(1, m, 3);
+        // The whole warp runs this loop converged (uniform operands, see ptx.cuh); one elected lane issues inside each
+        // wrapper.  Tiles of ALL items form one sequence g = 0, 1, ...: scores(g) are issued before the accumulate
+        // MMAs of tile g-1 even when g-1 belongs to the previous item.
+        constexpr uint32_t id_sc = ptx::umma_idesc_bf16(128, 64, 0, 0);     // scores: both operands K-major
+        constexpr uint32_t id_acc = ptx::umma_idesc_bf16(128, HD, 0, 1);    // accumulate: A from TMEM (K-major), B MN-major
+        int g = 0, k = 0;
+        // the tile whose accumulate MMAs are still to be issued
+        bool pend = false;
+        int p_g = 0, p_k = 0;
+        bool p_first = false, p_last = false;
+        auto accumulate = [&]() {
+            const int sm = p_g & 1, stm = p_g % NST, ap = p_k % AB;
+            const uint32_t b0 = sB0 + stm * C::STR, b1 = sB1 + stm * C::STR;
+            const uint32_t ta = tmem + sm * 128;             // bf16 P^T at +16*kk, dS^T (dS) at +64+16*kk
+            const uint32_t td = tmem + C::ACC + ap * (C::NACC * HD);
+            if (p_first) ptx::mbar_wait(acc_empty(ap), ((p_k / AB) & 1) ^ 1);     // drained by the epilogue of item p_k - AB
+            ptx::mbar_wait(out_full(sm), (p_g >> 1) & 1);
+            ptx::tc_fence_after();
+            if (p_k == 0) TRACE(1, p_g, 3);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {                 // contraction over the 64 streamed rows, 16 per MMA
-                    const uint32_t acc = (m > 0 || kk > 0) ? 1u : 0u;
-                    if (DKV) {
-                        // dV += P^T dO_i ; dK += dS^T Q_i      (A from TMEM, B = streamed tile read MN-major)
-                        ptx::mma_bf16_ts_w(tmem + C::ACC, ta + 16 * kk, ptx::umma_desc(b1 + kk * 2048, SUB64, 1024), id_acc, acc);
-                        ptx::mma_bf16_ts_w(tmem + C::ACC + HD, ta + 64 + 16 * kk, ptx::umma_desc(b0 + kk * 2048, SUB64, 1024),
-                                           id_acc, acc);
-                    } else {
-                        // dQ += dS K_j
-                        ptx::mma_bf16_ts_w(tmem + C::ACC, ta + 64 + 16 * kk, ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
-                    }
+            for (int kk = 0; kk < 4; ++kk) {                 // contraction over the 64 streamed rows, 16 per MMA
+                const uint32_t acc = (!p_first || kk > 0) ? 1u : 0u;
+                if (DKV) {
+                    // dV += P^T dO_i ; dK += dS^T Q_i      (A from TMEM, B = streamed tile read MN-major)
+                    ptx::mma_bf16_ts_w(td, ta + 16 * kk, ptx::umma_desc(b1 + kk * 2048, SUB64, 1024), id_acc, acc);
+                    ptx::mma_bf16_ts_w(td + HD, ta + 64 + 16 * kk, ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
+                } else {
+                    // dQ += dS K_j
+                    ptx::mma_bf16_ts_w(td, ta + 64 + 16 * kk, ptx::umma_desc(b0 + kk * 2048, SUB64, 1024), id_acc, acc);
                 }
-                ptx::mma_commit_w(str_empty(stm));
-                TRACE(1, m, 4);
-            };
-            ptx::mbar_wait(stat_full, 0);
-            for (int n = 0; n < niter; ++n) {
-                // scores of tile n first, so they run while the elementwise warps are still on tile n-1 ...
-                const int st = n % NST, s = n & 1;
+            }
+            ptx::mma_commit_w(str_empty(stm));
+            if (p_last) ptx::mma_commit_w(acc_full(ap));
+            if (p_k == 0) TRACE(1, p_g, 4);
+            pend = false;
+        };
+        for (int it = blockIdx.x; it < nitems; it += gridDim.x, ++k) {
+            const Item w = decode(it);
+            const int sp = k % SB;
+            if (SB == 1 && pend) accumulate();               // do not hold the last tile back behind a stationary reload
+            ptx::mbar_wait(stat_full(sp), (k / SB) & 1);
+            for (int n = 0; n < w.niter; ++n, ++g) {
+                const int st = g % NST, s = g & 1;
                 const uint32_t b0 = sB0 + st * C::STR, b1 = sB1 + st * C::STR;
-                ptx::mbar_wait(str_full(st), (n / NST) & 1);
-                TRACE(1, n, 0);
-                // scores stage s is free: its last readers were the accumulate MMAs of tile n-2, issued earlier by
+                ptx::mbar_wait(str_full(st), (g / NST) & 1);
+                if (k == 0) TRACE(1, n, 0);
+                // scores stage s is free: its last readers were the accumulate MMAs of tile g-2, issued earlier by
                 // this same warp, and tcgen05.mma executes in issue order
                 ptx::tc_fence_after();
-                TRACE(1, n, 1);
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk) {
                     const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
-                    ptx::mma_bf16_ss_w(tmem + s * 128, ptx::umma_desc(sA0 + oa, 16, 1024), ptx::umma_desc(b0 + ob, 16, 1024),
-                                     id_sc, kk > 0 ? 1u : 0u);
+                    ptx::mma_bf16_ss_w(tmem + s * 128, ptx::umma_desc(sA0(sp) + oa, 16, 1024), ptx::umma_desc(b0 + ob, 16, 1024),
+                                       id_sc, kk > 0 ? 1u : 0u);
                 }
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk) {
                     const uint32_t oa = (kk >> 2) * SUB + (kk & 3) * 32, ob = (kk >> 2) * SUB64 + (kk & 3) * 32;
-                    ptx::mma_bf16_ss_w(tmem + s * 128 + 64, ptx::umma_desc(sA1 + oa, 16, 1024), ptx::umma_desc(b1 + ob, 16, 1024),
-                                     id_sc, kk > 0 ? 1u : 0u);
+                    ptx::mma_bf16_ss_w(tmem + s * 128 + 64, ptx::umma_desc(sA1(sp) + oa, 16, 1024), ptx::umma_desc(b1 + ob, 16, 1024),
+                                       id_sc, kk > 0 ? 1u : 0u);
                 }
                 ptx::mma_commit_w(sc_full(s));
-                TRACE(1, n, 2);
-                // ... then the accumulation of tile n-1, whose out tiles they have just finished
-                if (n > 0) accumulate(n - 1);
+                if (n == w.niter - 1) ptx::mma_commit_w(stat_empty(sp));   // last reader of this item's stationary tiles
+                if (k == 0) TRACE(1, n, 2);
+                if (pend) accumulate();
+                pend = true; p_g = g; p_k = k; p_first = (n == 0); p_last = (n == w.niter - 1);
             }
-            accumulate(niter - 1);
-            ptx::mma_commit_w(acc_done);
         }
+        if (pend) accumulate();
     } else {
         // ------------------------------------------------------------------ elementwise warps (2..17)
-        // NPART warps share each TMEM lane quarter (tcgen05.ld reaches lanes 32*(warp%4)..+31): thread = stationary
-        // row, `part` = which slice of the 64 score columns.  The backward needs no row reductions (lse and delta
-        // are inputs), so the column split is free; 4 warps per scheduler hide the exp2 / LDS latencies.
-        // The 16 warps form two groups of 8 that take alternate tiles (group g owns score stage g), so the exp2-heavy
-        // middle of one tile overlaps the TMEM loads / stores / barrier hand-offs of the next one.
-        constexpr int NPART = BWD_EW_WARPS / 8, CPW = 64 / NPART;   // column parts per lane quarter within a group, columns per warp
+        // Four warps share each TMEM lane quarter (tcgen05.ld reaches lanes 32*(warp%4)..+31): thread = stationary row.
+        // Two groups of 8 warps take alternate tiles of the global tile sequence (group = score buffer); inside a
+        // group a warp owns 32 of the 64 score columns.  The backward needs no row reductions (lse and delta are
+        // inputs), so the column split is free.
+        constexpr int CPW = 32;
         const int q = warp & 3;
         const int grp = (warp - 2) >> 3;
         const int part = ((warp - 2) >> 2) & 1;
         const int row = q * 32 + lane;
-        const int srow = r0 + row;                                  // key row (DKV) / query row (DQ)
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-        float my_l2 = INFINITY, my_dl = 0.f;
-        if (!DKV && srow < T) { my_l2 = lse_g[srow] * 1.4426950408889634f; my_dl = del_g[srow]; }
-        for (int n = grp; n < niter; n += 2) {
-            const int s = n & 1, ph = (n >> 1) & 1;
-            const int c0 = (it0 + n) * 64;                          // first streamed row = first score column
-            const float* vl = s_vec + (n % NST) * 128;
-            // causal mask is needed only where the streamed tile overlaps the diagonal
-            const bool need_mask = DKV ? (c0 < r0 + 128) : (c0 + 63 > r0);
-            if (warp == 2 && lane == 0) TRACE(2, n, 0);
-            if (DKV) ptx::mbar_wait(vec_full(n % NST), (n / NST) & 1);
-            if (warp == 2 && lane == 0) TRACE(2, n, 1);
-            ptx::mbar_wait(sc_full(s), ph);
-            ptx::tc_fence_after();
-            if (warp == 2 && lane == 0) TRACE(2, n, 2);
-            if (warp == 2 && lane == 0) TRACE(2, n, 3);
-            // MASKED is a compile-time flag so the 7-of-9 off-diagonal tiles carry no compare/select instructions
-            auto tile = [&](auto masked_tag) {
-                constexpr bool MASKED = decltype(masked_tag)::value;
+        int g = 0, k = 0;
+        for (int it = blockIdx.x; it < nitems; it += gridDim.x, ++k) {
+            const Item w = decode(it);
+            const int srow = w.r0 + row;                                 // key row (DKV) / query row (DQ)
+            const float* lse_g = lse + ((size_t)w.b * H + w.h) * T;
+            const float* del_g = delta + ((size_t)w.b * H + w.h) * T;
+            float my_l2 = INFINITY, my_dl = 0.f;
+            if (!DKV && srow < T) { my_l2 = lse_g[srow] * 1.4426950408889634f; my_dl = del_g[srow]; }
+            for (int n = 0; n < w.niter; ++n, ++g) {
+                if ((g & 1) != grp) continue;
+                const int s = g & 1, ph = (g >> 1) & 1;
+                const int c0 = (w.it0 + n) * 64;                         // first streamed row = first score column
+                const float* vl = s_vec + (g % NST) * 128;
+                // causal mask is needed only where the streamed tile overlaps the diagonal
+                const bool need_mask = DKV ? (c0 < w.r0 + 128) : (c0 + 63 > w.r0);
+                if (k == 0 && warp == 2 && lane == 0) TRACE(2, n, 0);
+                if (DKV) ptx::mbar_wait(vec_full(g % NST), (g / NST) & 1);
+                ptx::mbar_wait(sc_full(s), ph);
+                ptx::tc_fence_after();
+                if (k == 0 && warp == 2 && lane == 0) TRACE(2, n, 2);
+                // MASKED is a compile-time flag so the 7-of-9 off-diagonal tiles carry no compare/select instructions
+                auto tile = [&](auto masked_tag) {
+                    constexpr bool MASKED = decltype(masked_tag)::value;
 #pragma unroll
-                for (int c = 0; c < CPW / 16; ++c) {
-                    const int cb = part * CPW + c * 16;             // first score column of this 16-wide piece
-                    uint32_t rs[16], rp[16];
-                    ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + cb, rs);
-                    ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + 64 + cb, rp);
-                    ptx::tmem_ld_wait();
-                    uint32_t pk[8], dk[8];
+                    for (int c = 0; c < CPW / 16; ++c) {
+                        const int cb = part * CPW + c * 16;             // first score column of this 16-wide piece
+                        uint32_t rs[16], rp[16];
+                        ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + cb, rs);
+                        ptx::tmem_ld_32x16(tmem + lane_off + s * 128 + 64 + cb, rp);
+                        ptx::tmem_ld_wait();
+                        uint32_t pk[8], dk[8];
 #pragma unroll
-                    for (int e = 0; e < 16; e += 2) {
-                        const int col = cb + e;
-                        const float l2a = DKV ? vl[col] : my_l2, l2b = DKV ? vl[col + 1] : my_l2;
-                        const float dla = DKV ? vl[64 + col] : my_dl, dlb = DKV ? vl[64 + col + 1] : my_dl;
-                        // Rows / columns past T need no extra test: TMA zero-fills them, out-of-range QUERIES carry
-                        // lse = +inf (p = 0), and out-of-range KEYS are either masked by causality or only feed
-                        // output rows that are never stored.
-                        float p0 = exp2f(__uint_as_float(rs[e]) * scale_log2 - l2a);
-                        float p1 = exp2f(__uint_as_float(rs[e + 1]) * scale_log2 - l2b);
-                        if (MASKED) {
-                            // key index must be <= query index
-                            const int key0 = DKV ? srow : c0 + col, qry0 = DKV ? c0 + col : srow;
-                            if (key0 > qry0) p0 = 0.f;
-                            if (DKV ? (key0 > qry0 + 1) : (key0 + 1 > qry0)) p1 = 0.f;
+                        for (int e = 0; e < 16; e += 2) {
+                            const int col = cb + e;
+                            const float l2a = DKV ? vl[col] : my_l2, l2b = DKV ? vl[col + 1] : my_l2;
+                            const float dla = DKV ? vl[64 + col] : my_dl, dlb = DKV ? vl[64 + col + 1] : my_dl;
+                            // Rows / columns past T need no extra test: TMA zero-fills them, out-of-range QUERIES carry
+                            // lse = +inf (p = 0), and out-of-range KEYS are either masked by causality or only feed
+                            // output rows that are never stored.
+                            float p0 = exp2f(__uint_as_float(rs[e]) * scale_log2 - l2a);
+                            float p1 = exp2f(__uint_as_float(rs[e + 1]) * scale_log2 - l2b);
+                            if (MASKED) {
+                                // key index must be <= query index
+                                const int key0 = DKV ? srow : c0 + col, qry0 = DKV ? c0 + col : srow;
+                                if (key0 > qry0) p0 = 0.f;
+                                if (DKV ? (key0 > qry0 + 1) : (key0 + 1 > qry0)) p1 = 0.f;
+                            }
+                            const float s0 = p0 * (__uint_as_float(rp[e]) - dla);
+                            const float s1 = p1 * (__uint_as_float(rp[e + 1]) - dlb);
+                            if (DKV) pk[e >> 1] = pack_bf16x2(p0, p1);
+                            dk[e >> 1] = pack_bf16x2(s0, s1);
                         }
-                        // the 1/sqrt(hs) factor of dS is applied once per output element in the epilogue
-                        const float s0 = p0 * (__uint_as_float(rp[e]) - dla);
-                        const float s1 = p1 * (__uint_as_float(rp[e + 1]) - dlb);
-                        if (DKV) pk[e >> 1] = pack_bf16x2(p0, p1);
-                        dk[e >> 1] = pack_bf16x2(s0, s1);
+                        // bf16 results go back into the first 8 of the 16 TMEM columns this warp just read: they are the
+                        // K=16 slice number cb/16 of the A operand of the accumulate MMAs (2 bf16 per 32-bit column)
+                        if (DKV) ptx::tmem_st_32x8(tmem + lane_off + s * 128 + cb, pk);
+                        ptx::tmem_st_32x8(tmem + lane_off + s * 128 + 64 + cb, dk);
                     }
-                    // bf16 results go back into the first 8 of the 16 TMEM columns this warp just read: they are the
-                    // K=16 slice number cb/16 of the A operand of the accumulate MMAs (2 bf16 per 32-bit column)
-                    if (DKV) ptx::tmem_st_32x8(tmem + lane_off + s * 128 + cb, pk);
-                    ptx::tmem_st_32x8(tmem + lane_off + s * 128 + 64 + cb, dk);
+                };
+                if (need_mask) tile(MaskOn{}); else tile(MaskOff{});
+                if (k == 0 && warp == 2 && lane == 0) TRACE(2, n, 4);
+                ptx::tmem_st_wait();
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(out_full(s));
+                if (k == 0 && warp == 2 && lane == 0) TRACE(2, n, 5);
+            }
+            // ---- epilogue of this item: accumulator rows -> bf16 -> dqkv (thread = stationary row; the four warps of a
+            //      lane quarter take every fourth 16-column piece)
+            const int ap = k % AB;
+            ptx::mbar_wait(acc_full(ap), (k / AB) & 1);
+            ptx::tc_fence_after();
+            const uint32_t td = tmem + lane_off + C::ACC + ap * (C::NACC * HD);
+            bf16* g0 = dqkv + ((size_t)w.b * T + srow) * (3 * d_model) + w.h * HD + (DKV ? 2 * d_model : 0);   // dV | dQ
+            bf16* g1 = dqkv + ((size_t)w.b * T + srow) * (3 * d_model) + w.h * HD + d_model;                    // dK
+            const float f0 = DKV ? 1.f : scale;
+#pragma unroll 1
+            for (int c = part + 2 * grp; c < HD / 16; c += 4) {
+                uint32_t r0v[16], r1v[16];
+                ptx::tmem_ld_32x16(td + c * 16, r0v);
+                if (DKV) ptx::tmem_ld_32x16(td + HD + c * 16, r1v);
+                ptx::tmem_ld_wait();
+                if (srow < T) {
+#pragma unroll
+                    for (int e = 0; e < 16; e += 8) {
+                        *reinterpret_cast<uint4*>(g0 + c * 16 + e) =
+                            make_uint4(pack_bf16x2(f0 * __uint_as_float(r0v[e]), f0 * __uint_as_float(r0v[e + 1])),
+                                       pack_bf16x2(f0 * __uint_as_float(r0v[e + 2]), f0 * __uint_as_float(r0v[e + 3])),
+                                       pack_bf16x2(f0 * __uint_as_float(r0v[e + 4]), f0 * __uint_as_float(r0v[e + 5])),
+                                       pack_bf16x2(f0 * __uint_as_float(r0v[e + 6]), f0 * __uint_as_float(r0v[e + 7])));
+                        if (DKV)
+                            *reinterpret_cast<uint4*>(g1 + c * 16 + e) =
+                                make_uint4(pack_bf16x2(scale * __uint_as_float(r1v[e]), scale * __uint_as_float(r1v[e + 1])),
+                                           pack_bf16x2(scale * __uint_as_float(r1v[e + 2]), scale * __uint_as_float(r1v[e + 3])),
+                                           pack_bf16x2(scale * __uint_as_float(r1v[e + 4]), scale * __uint_as_float(r1v[e + 5])),
+                                           pack_bf16x2(scale * __uint_as_float(r1v[e + 6]), scale * __uint_as_float(r1v[e + 7])));
+                    }
                 }
-            };
-            if (need_mask) tile(MaskOn{}); else tile(MaskOff{});
-            if (warp == 2 && lane == 0) TRACE(2, n, 4);
-            ptx::tmem_st_wait();
+            }
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(out_full(s));
-            if (warp == 2 && lane == 0) TRACE(2, n, 5);
-        }
-        // ---- epilogue: accumulator rows -> bf16 -> dqkv (thread = stationary row, warp half = alternate 16-col pieces)
-        if (niter > 0) {
-            ptx::mbar_wait(acc_done, 0);
-            ptx::tc_fence_after();
-        }
-        bf16* g0 = dqkv + ((size_t)b * T + srow) * (3 * d_model) + h * HD + (DKV ? 2 * d_model : 0);   // dV | dQ
-        bf16* g1 = dqkv + ((size_t)b * T + srow) * (3 * d_model) + h * HD + d_model;                    // dK
-        const float f0 = DKV ? 1.f : scale;
-#pragma unroll 1
-        for (int c = part + 2 * grp; c < HD / 16; c += 2 * NPART) {
-            uint32_t r0v[16], r1v[16];
-            if (niter > 0) {
-                ptx::tmem_ld_32x16(tmem + lane_off + C::ACC + c * 16, r0v);
-                if (DKV) ptx::tmem_ld_32x16(tmem + lane_off + C::ACC + HD + c * 16, r1v);
-                ptx::tmem_ld_wait();
-            } else {
-#pragma unroll
-                for (int e = 0; e < 16; ++e) { r0v[e] = 0u; r1v[e] = 0u; }
-            }
-            if (srow < T) {
-#pragma unroll
-                for (int e = 0; e < 16; e += 8) {
-                    *reinterpret_cast<uint4*>(g0 + c * 16 + e) =
-                        make_uint4(pack_bf16x2(f0 * __uint_as_float(r0v[e]), f0 * __uint_as_float(r0v[e + 1])),
-                                   pack_bf16x2(f0 * __uint_as_float(r0v[e + 2]), f0 * __uint_as_float(r0v[e + 3])),
-                                   pack_bf16x2(f0 * __uint_as_float(r0v[e + 4]), f0 * __uint_as_float(r0v[e + 5])),
-                                   pack_bf16x2(f0 * __uint_as_float(r0v[e + 6]), f0 * __uint_as_float(r0v[e + 7])));
-                    if (DKV)
-                        *reinterpret_cast<uint4*>(g1 + c * 16 + e) =
-                            make_uint4(pack_bf16x2(scale * __uint_as_float(r1v[e]), scale * __uint_as_float(r1v[e + 1])),
-                                       pack_bf16x2(scale * __uint_as_float(r1v[e + 2]), scale * __uint_as_float(r1v[e + 3])),
-                                       pack_bf16x2(scale * __uint_as_float(r1v[e + 4]), scale * __uint_as_float(r1v[e + 5])),
-                                       pack_bf16x2(scale * __uint_as_float(r1v[e + 6]), scale * __uint_as_float(r1v[e + 7])));
-                }
-            }
+            if (lane == 0) ptx::mbar_arrive(acc_empty(ap));
         }
     }
     ptx::tc_fence_before();
@@ -691,7 +718,9 @@ int launch_bwd_pass(const CUtensorMap& t128, const CUtensorMap& t64, const CUten
         cfg = true;
     }
     const int ntile = (T + 127) / 128;
-    B200_CHECK_CUDA(b200_launch(kern, dim3(ntile * H * B), dim3(NTHREADS_BWD), C::SMEM, st, t128, t64, d128, d64, lse, delta,
+    const int nitems = ntile * H * B;
+    const int grid = nitems < b200_num_sms() ? nitems : b200_num_sms();
+    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NTHREADS_BWD), C::SMEM, st, t128, t64, d128, d64, lse, delta,
                                 (bf16*)dqkv, T, H, H * B, ntile, scale, scale * 1.4426950408889634f));
     return 0;
 }
