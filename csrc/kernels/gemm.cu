@@ -242,8 +242,8 @@ extern "C" int b200_gemm_pick_bn(int M, int N, int K, int out_f32) {
 
 extern "C" int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
                          long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha,
-                         const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn_override,
-                         int split_k, cudaStream_t st) {
+                         const float* bias, int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out,
+                         const void* relu_bits, int bn_override, int split_k, cudaStream_t st) {
     B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
     B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda/ldb must be multiples of 8 elements (16 bytes)");
     B200_REQUIRE(out_f32 ? (ldc % 4 == 0 && N % 4 == 0) : (ldc % 8 == 0), "gemm: bad ldc / N alignment");
@@ -272,6 +272,7 @@ extern "C" int b200_gemm(const void* A, const void* B, void* C, int M, int N, in
     B200_REQUIRE(splits == 1 || (out_f32 && f32_mode == 2), "gemm: split-K needs the atomic fp32 epilogue");
     p.alpha = alpha;
     p.bias = bias; p.relu = relu; p.mask = (const bf16*)mask; p.ld_mask = ld_mask; p.stats = (float2*)stats;
+    p.relu_bits_out = (unsigned long long*)relu_bits_out; p.relu_bits = (const unsigned long long*)relu_bits;
     p.out_f32 = (float*)C; p.ldc = ldc; p.f32_mode = f32_mode;
 
     CUtensorMap tA, tB, tC;

@@ -280,7 +280,8 @@ int launch2_major(int a_mn, int b_mn, const CUtensorMap& tA, const CUtensorMap& 
 // Same contract as b200_gemm, tiles of 256 x bn (bn = 256 or 128) on CTA pairs.
 extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, int N, int K, long long lda, long long ldb,
                               long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias,
-                              int relu, const void* mask, int ld_mask, void* stats, int bn, int split_k, cudaStream_t st) {
+                              int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out,
+                         const void* relu_bits, int bn, int split_k, cudaStream_t st) {
     B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_2cta: empty problem");
     B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_2cta: lda/ldb must be multiples of 8 elements");
     B200_REQUIRE(out_f32 ? (ldc % 4 == 0 && N % 4 == 0) : (ldc % 8 == 0), "gemm_2cta: bad ldc / N alignment");
@@ -306,6 +307,7 @@ extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, i
     B200_REQUIRE(splits == 1 || (out_f32 && f32_mode == 2), "gemm_2cta: split-K needs the atomic fp32 epilogue");
     p.alpha = alpha;
     p.bias = bias; p.relu = relu; p.mask = (const bf16*)mask; p.ld_mask = ld_mask; p.stats = (float2*)stats;
+    p.relu_bits_out = (unsigned long long*)relu_bits_out; p.relu_bits = (const unsigned long long*)relu_bits;
     p.out_f32 = (float*)Cout; p.ldc = ldc; p.f32_mode = f32_mode;
 
     CUtensorMap tA, tB, tC;
@@ -333,7 +335,8 @@ extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, i
 // gather != 0: this launch also pulls every remote chunk of the layer from h_wb[peer] into h_wb[rank]
 // (the first weight-consuming GEMM of the layer); later GEMMs of the layer only wait on the flags.
 extern "C" int b200_gemm_ag(const void* A, void* Cout, int M, int N, int K, long long lda, long long ldc, const float* bias,
-                            int relu, void* const* h_wb, int world, int rank, long long layer_start, long long layer_end,
+                            int relu, void* relu_bits_out, void* const* h_wb, int world, int rank, long long layer_start,
+                            long long layer_end,
                             long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev,
                             int gather, cudaStream_t st) {
     B200_REQUIRE(world >= 1 && world <= 8, "gemm_ag: world size %d not supported", world);
@@ -347,7 +350,7 @@ extern "C" int b200_gemm_ag(const void* A, void* Cout, int M, int N, int K, long
     p.num_n = (N + BN - 1) / BN;
     p.num_kb = (K + BK - 1) / BK;
     p.splits = 1; p.kb_per_split = p.num_kb;
-    p.alpha = 1.f; p.bias = bias; p.relu = relu;
+    p.alpha = 1.f; p.bias = bias; p.relu = relu; p.relu_bits_out = (unsigned long long*)relu_bits_out;
     // start with the n-tiles whose weight rows this rank owns
     const long long own = layer_start + (long long)rank * chunk - w_offset;
     if (own > 0 && own < (long long)N * K) p.n_shift = (int)(((own + K - 1) / K + BN - 1) / BN) % p.num_n;

@@ -22,6 +22,12 @@ struct Params {
     const bf16* mask;       // [M, ld_mask] post-ReLU activations: out = mask > 0 ? v : 0
     int ld_mask;
     float2* stats;          // [num_n][M] (max, sum exp) of the bf16-rounded outputs, or null
+    // ReLU sign bits, one 64-bit word per (row, 64-column chunk): [M][ceil(N/64)].  The forward GEMM that applies the
+    // ReLU writes them (bit j = bf16 output column 64*w + j is > 0); the matching dgrad GEMM reads them back instead of
+    // the activations: 32 B per row and 256-column tile instead of 512 B, and no uncoalesced 16-byte loads (a dgrad with
+    // the activation mask ran 2.5x slower than without: 32 LSU wavefronts per mask load instruction).
+    unsigned long long* relu_bits_out;
+    const unsigned long long* relu_bits;
     // fp32 epilogue
     float* out_f32;
     long long ldc;
@@ -59,6 +65,14 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
         asm volatile("bar.sync 1, 128;" ::: "memory");          // previous tile's readers are done
         for (int j = et; j < BN; j += 128) s_bias[j] = (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
         asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+    // ReLU sign bits of this row for the whole tile: loaded while the MMAs are still running
+    const int ld_bits = (p.N + 63) >> 6;
+    unsigned long long mbits[BN / 64];
+    if (!OUT_F32 && p.relu_bits != nullptr) {
+#pragma unroll
+        for (int c = 0; c < BN / 64; ++c)
+            mbits[c] = (m < p.M && (n0 >> 6) + c < ld_bits) ? __ldg(p.relu_bits + (size_t)m * ld_bits + (n0 >> 6) + c) : 0ull;
     }
     ptx::mbar_wait(tfull_bar, acc_phase);
     ptx::tc_fence_after();
@@ -143,11 +157,32 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
                     }
                 }
             }
+            if (p.relu_bits != nullptr) {
+                const uint32_t lo = (uint32_t)mbits[c], hi = (uint32_t)(mbits[c] >> 32);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    if (!(lo & (1u << j))) r[j] = 0u;
+                    if (!(hi & (1u << j))) r[32 + j] = 0u;
+                }
+            }
             // ---- pack to bf16
             uint32_t pk[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j)
                 pk[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+            if (p.relu_bits_out != nullptr) {
+                // sign bits of the bf16-ROUNDED outputs (what the activation tensor holds); after the ReLU they are >= 0
+                uint32_t lo = 0u, hi = 0u;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    if (pk[j] & 0x00007fffu) lo |= 1u << (2 * j);
+                    if (pk[j] & 0x7fff0000u) lo |= 1u << (2 * j + 1);
+                    if (pk[16 + j] & 0x00007fffu) hi |= 1u << (2 * j);
+                    if (pk[16 + j] & 0x7fff0000u) hi |= 1u << (2 * j + 1);
+                }
+                if (m < p.M && nc0 < p.N)
+                    p.relu_bits_out[(size_t)m * ld_bits + (nc0 >> 6)] = ((unsigned long long)hi << 32) | lo;
+            }
             if (p.stats != nullptr) {
                 // online softmax statistics over the bf16-rounded values (what CE will see)
                 float cmax = -INFINITY;

@@ -67,11 +67,11 @@ int b200_ln_bwd_static(const void* dy, const float* x, const float* mean, const 
  * out_f32 = 1: C fp32, f32_mode 0 store / 1 accumulate / 2 atomic add (enables split-K;
  *              split_k = 0 picks automatically, C must then hold the running sum). */
 int b200_gemm_pick_bn(int M, int N, int K, int out_f32);
-int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn_override, int split_k, cudaStream_t st);
+int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out, const void* relu_bits, int bn_override, int split_k, cudaStream_t st);
 
 /* Same contract on CTA pairs (tcgen05 cta_group::2, cluster of 2): tiles of 256 x bn (bn = 256 | 128), each CTA
  * stages half of the operands, 6-8 pipeline stages.  The default for large problems. */
-int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, int bn, int split_k, cudaStream_t st);
+int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out, const void* relu_bits, int bn, int split_k, cudaStream_t st);
 
 /* All-gather fused into the forward GEMM (sharded data parallelism, ref: absent in the reference - SURVEY N6/T11):
  * C[M,N] = A[M,K] * W^T (+bias) (ReLU), W [N,K] = a slot of the flat bf16 weight buffer at element w_offset inside
@@ -79,7 +79,7 @@ int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, l
  * peer-mapped flat weight buffers.  flags / counters: [world] ints on this device, zero-initialised once.
  * gather != 0: this launch's extra warps pull every remote chunk of the layer over NVLink into the local buffer and
  * raise flags[c] = *epoch_dev; tiles whose rows are already local run meanwhile, the others wait per chunk. */
-int b200_gemm_ag(const void* A, void* C, int M, int N, int K, long long lda, long long ldc, const float* bias, int relu, void* const* h_wb, int world, int rank, long long layer_start, long long layer_end, long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev, int gather, cudaStream_t st);
+int b200_gemm_ag(const void* A, void* C, int M, int N, int K, long long lda, long long ldc, const float* bias, int relu, void* relu_bits_out, void* const* h_wb, int world, int rank, long long layer_start, long long layer_end, long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev, int gather, cudaStream_t st);
 
 /* Weight-streaming GEMM for decode-sized batches (M <= 128): out[M,N] = act(x[M,K] @ W[N,K]^T + bias), operands
  * swapped so the weight tile is the 128-row MMA operand; K is split over the CTAs of a thread-block cluster

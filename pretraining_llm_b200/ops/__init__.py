@@ -47,12 +47,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
          b_mn: bool = False, out_dtype=BF16, f32_mode: int = 0, alpha: float = 1.0,
          bias: Optional[torch.Tensor] = None, relu: bool = False, mask: Optional[torch.Tensor] = None,
          stats: Optional[torch.Tensor] = None, bn: int = 0, split_k: int = 0,
-         two_cta: Optional[bool] = None) -> torch.Tensor:
+         two_cta: Optional[bool] = None, relu_bits_out: Optional[torch.Tensor] = None,
+         relu_bits: Optional[torch.Tensor] = None) -> torch.Tensor:
     """C[M,N] = alpha * opA @ opB^T on the tcgen05 kernel.
 
     a: [M,K] (a_mn=False) or [K,M] (a_mn=True); b: [N,K] (b_mn=False) or [K,N] (b_mn=True); bf16,
     last dim contiguous.  out bf16 (epilogue: +bias, ReLU, *(mask>0), softmax stats) or fp32
-    (f32_mode 0 store / 1 accumulate / 2 atomic+split-K)."""
+    (f32_mode 0 store / 1 accumulate / 2 atomic+split-K).
+    relu_bits_out / relu_bits: int64 [M, ceil(N/64)] sign bits of the ReLU output, written by the forward GEMM and
+    applied by the matching dgrad GEMM (the fast replacement of mask=activations)."""
     assert a.dtype == BF16 and b.dtype == BF16 and a.stride(-1) == 1 and b.stride(-1) == 1
     if a_mn:
         K, M = a.shape
@@ -70,6 +73,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     assert out.shape == (M, N) and out.stride(-1) == 1
     out_f32 = out.dtype == F32
     assert out_f32 or out.dtype == BF16
+    for t in (relu_bits_out, relu_bits):
+        assert t is None or (t.dtype == torch.int64 and t.is_contiguous() and t.shape == (M, (N + 63) // 64))
     L = lib.load()
     if two_cta is None:
         two_cta = GEMM_2CTA and M >= 512 and N >= 256 and bn in (0, 128, 256)
@@ -86,7 +91,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
             f32_mode, split_k = 2, 2
     rc = fn(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
             int(a_mn), int(b_mn), int(out_f32), f32_mode, float(alpha), _p(bias), int(relu),
-            _p(mask), 0 if mask is None else mask.stride(0), _p(stats), bn, split_k, _st())
+            _p(mask), 0 if mask is None else mask.stride(0), _p(stats), _p(relu_bits_out), _p(relu_bits), bn, split_k,
+            _st())
     _chk(rc, "gemm")
     return out
 

@@ -192,7 +192,7 @@ class DataParallel:
 
     # ------------------------------------------------------------------ sharded weights ("zero" mode)
     def gemm_ag(self, layer: int, slot_name: str, a: torch.Tensor, out: torch.Tensor, bias=None, relu: bool = False,
-                gather: bool = False) -> None:
+                gather: bool = False, relu_bits_out=None) -> None:
         """Forward GEMM of a block whose weight matrix is sharded across the ranks: the all-gather of the layer's
         weights is fused into the (first) GEMM that consumes them (csrc/kernels/gemm2.cu, b200_gemm_ag)."""
         lay = self.eng.layout
@@ -201,7 +201,8 @@ class DataParallel:
         N, K = slot.shape
         M = a.shape[0]
         rc = lib.load().b200_gemm_ag(a.data_ptr(), out.data_ptr(), M, N, K, a.stride(0), out.stride(0),
-                                     None if bias is None else bias.data_ptr(), int(relu), self.sym_wb.ptr_array,
+                                     None if bias is None else bias.data_ptr(), int(relu),
+                                     None if relu_bits_out is None else relu_bits_out.data_ptr(), self.sym_wb.ptr_array,
                                      self.world, self.rank, plan.start, plan.end, plan.chunk, slot.offset,
                                      self.ag_flags[layer].data_ptr(), self.ag_counters[layer].data_ptr(),
                                      self.version_dev.data_ptr(), int(gather), torch.cuda.current_stream().cuda_stream)

@@ -52,6 +52,8 @@ class Workspace:
         self.qkv = e(Ls, M, 3 * d)
         self.att = e(Ls, M, d)
         self.act = e(Ls, M, 4 * d)
+        # sign bits of the ReLU outputs (one int64 per row and 64 columns): what the MLP dgrad epilogue masks with
+        self.relu_bits = torch.empty(Ls, M, (4 * d + 63) // 64, device=dev, dtype=torch.int64)
         self.mlp_out = e(M, d)
         self.lse = e(Ls, B, H, T, dt=F32)
         self.ln_stats = e(2 * Ls + 1, 2, M, dt=F32)  # (mean, rstd) for ln1/ln2 of each layer + final
@@ -169,11 +171,11 @@ class Engine:
                        x_out=w.resid_b[s], out=w.h2[s], mean=st2[0], rstd=st2[1])
             if zero:
                 self.dp.gemm_ag(l, pre + "mlp.hidden.weight", w.h2[s], w.act[s], bias=self.P(pre + "mlp.hidden.bias"),
-                                relu=True)
+                                relu=True, relu_bits_out=w.relu_bits[s] if w.train else None)
                 self.dp.gemm_ag(l, pre + "mlp.proj.weight", w.act[s], w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
             else:
                 ops.gemm(w.h2[s], self.W(pre + "mlp.hidden.weight"), out=w.act[s],
-                         bias=self.P(pre + "mlp.hidden.bias"), relu=True)
+                         bias=self.P(pre + "mlp.hidden.bias"), relu=True, relu_bits_out=w.relu_bits[s] if w.train else None)
                 ops.gemm(w.act[s], self.W(pre + "mlp.proj.weight"), out=w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
         sl = (L - 1) if w.train else 0
         sf = L if w.train else 1
@@ -247,7 +249,7 @@ class Engine:
             st1, st2 = w.ln_stats[2 * l], w.ln_stats[2 * l + 1]
             # ---- MLP
             ops.gemm(w.dx_bf16, w.act[l], out=self.G(pre + "mlp.proj.weight"), a_mn=True, b_mn=True, f32_mode=fm)
-            ops.gemm(w.dx_bf16, self.W(pre + "mlp.proj.weight"), out=w.dh, b_mn=True, mask=w.act[l])
+            ops.gemm(w.dx_bf16, self.W(pre + "mlp.proj.weight"), out=w.dh, b_mn=True, relu_bits=w.relu_bits[l])
             ops.colsum(w.dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
             ops.gemm(w.dh, w.h2[l], out=self.G(pre + "mlp.hidden.weight"), a_mn=True, b_mn=True, f32_mode=fm)
             ops.gemm(w.dh, self.W(pre + "mlp.hidden.weight"), out=w.dtmp, b_mn=True)

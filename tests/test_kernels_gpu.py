@@ -96,6 +96,32 @@ def test_gemm_epilogues(ops):
     assert _rel(c2, ref2) < 6e-3
 
 
+@pytest.mark.parametrize("two_cta", [False, True])
+@pytest.mark.parametrize("shape", [(512, 1024, 256), (300, 200, 128), (640, 3072, 768)])
+def test_gemm_relu_sign_bits(ops, two_cta, shape):
+    """Forward GEMM (+bias, ReLU) writes one sign bit per output; the dgrad GEMM masks with them."""
+    torch.manual_seed(4)
+    M, N, K = shape
+    a, b = _rand(M, K), _rand(N, K, scale=0.1)
+    bias = torch.randn(N, device="cuda")
+    bits = torch.zeros(M, (N + 63) // 64, device="cuda", dtype=torch.int64)
+    act = ops.gemm(a, b, bias=bias, relu=True, relu_bits_out=bits, two_cta=two_cta)
+    # bit j of word w of row m  <->  act[m, 64 w + j] > 0
+    cols = torch.arange(N, device="cuda")
+    got = ((bits[:, cols // 64] >> (cols % 64)) & 1).bool()
+    assert torch.equal(got, act > 0)
+    # unused high bits of the last word stay clear
+    if N % 64:
+        assert int((bits[:, -1] >> (N % 64)).abs().max()) == 0
+    # dgrad: dH[M, N] = (dOut[M, P] @ W2[P, N]) * (act > 0)
+    P = 256
+    dout, w2 = _rand(M, P), _rand(P, N, scale=0.1)
+    dh = ops.gemm(dout, w2, b_mn=True, relu_bits=bits, two_cta=two_cta)
+    ref = (dout.float() @ w2.float()) * (act > 0)
+    assert _rel(dh, ref) < 6e-3
+    assert torch.equal(dh == 0, ~(act > 0) | (dh == 0))
+
+
 @pytest.mark.parametrize("bn", [64, 128, 256])
 def test_gemm_nt_dgrad(ops, bn):
     """dX[M,K] = dY[M,N] @ W[N,K]: B operand MN-major."""
