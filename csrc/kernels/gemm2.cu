@@ -194,14 +194,24 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         int acc = 0;
         uint32_t acc_phase = 0;
         int buf = 0;
+        const int et = (int)threadIdx.x - 64;
+        auto n0_of = [&](int u) { return ((((u % ntiles) / p.num_m) + p.n_shift) % p.num_n) * BN; };
+        float bias_pf[(BN + 127) / 128];
+#pragma unroll
+        for (int i = 0; i < (BN + 127) / 128; ++i) {
+            const int j = et + 128 * i;
+            bias_pf[i] = (!OUT_F32 && p.bias != nullptr && pair < nunits && j < BN && n0_of(pair) + j < p.N)
+                             ? __ldg(p.bias + n0_of(pair) + j) : 0.f;
+        }
         for (int u = pair; u < nunits; u += npairs) {
             const int tile = u % ntiles;
             const int n_blk = ((tile / p.num_m) + p.n_shift) % p.num_n;
             const int m0 = (tile % p.num_m) * 256 + (int)rank * 128, n0 = n_blk * BN;
+            const int n0_next = (u + npairs < nunits) ? n0_of(u + npairs) : -1;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
             const uint32_t te = ptx::mapa(tempty_bar(acc), 0);   // the leader's accumulator-empty barrier
             gemm::epilogue_tile<BN, OUT_F32>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base,
-                                             buf, store_thread, s_bias, (int)threadIdx.x - 64,
+                                             buf, store_thread, s_bias, et, bias_pf, n0_next,
                                              [te]() { ptx::mbar_arrive_cluster(te); });
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }

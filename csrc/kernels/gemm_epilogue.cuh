@@ -54,16 +54,23 @@ struct AgParams {
 
 // tfull_bar: local mbarrier (shared::cta address) the MMA issuer commits to; taddr: TMEM address of this
 // thread's lane quarter at the accumulator stage's first column; m0: first global row of this CTA's 128 rows.
+// bias_pf: this thread's share of the CURRENT tile's bias slice, loaded one tile ahead (n0_next: first column of the
+// next tile of this CTA, < 0 if none) so the global-load latency never sits in front of a tile's epilogue.
 template <int BN, bool OUT_F32, class ArriveFn>
 __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap* tmC, uint32_t tfull_bar, uint32_t acc_phase,
                                               uint32_t taddr, int m0, int n0, int n_blk, int row, int lane,
                                               uint32_t epi_base, int& buf, bool store_thread, float* s_bias, int et,
-                                              ArriveFn arrive_tempty) {
+                                              float (&bias_pf)[(BN + 127) / 128], int n0_next, ArriveFn arrive_tempty) {
     const int m = m0 + row;
     if (!OUT_F32 && p.bias != nullptr) {
         // stage this tile's bias slice in smem while the MMAs are still running
         asm volatile("bar.sync 1, 128;" ::: "memory");          // previous tile's readers are done
-        for (int j = et; j < BN; j += 128) s_bias[j] = (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+#pragma unroll
+        for (int i = 0; i < (BN + 127) / 128; ++i) {
+            const int j = et + 128 * i;
+            if (j < BN) s_bias[j] = bias_pf[i];
+            bias_pf[i] = (n0_next >= 0 && j < BN && n0_next + j < p.N) ? __ldg(p.bias + n0_next + j) : 0.f;
+        }
         asm volatile("bar.sync 1, 128;" ::: "memory");
     }
     // ReLU sign bits of this row for the whole tile: loaded while the MMAs are still running
@@ -185,29 +192,52 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
             }
             if (p.stats != nullptr) {
                 // online softmax statistics over the bf16-rounded values (what CE will see)
-                float cmax = -INFINITY;
+                if (nc0 + 64 <= p.N) {
+                    // full chunk (all but the last of the vocabulary): packed bf16x2 maximum, then exp2 with four
+                    // independent accumulators.  (The per-element bounds tests and the serial sum of the general
+                    // path made the LM-head epilogue as long as its main loop.)
+                    bf162 mx2 = *reinterpret_cast<const bf162*>(&pk[0]);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    float2 f = unpack_bf16x2(pk[j]);
-                    if (nc0 + 2 * j < p.N) cmax = fmaxf(cmax, f.x);
-                    if (nc0 + 2 * j + 1 < p.N) cmax = fmaxf(cmax, f.y);
-                }
-                const float new_max = fmaxf(run_max, cmax);
-                if (new_max > -INFINITY) {
-                    float s = 0.f;
+                    for (int j = 1; j < 32; ++j) mx2 = __hmax2(mx2, *reinterpret_cast<const bf162*>(&pk[j]));
+                    const float2 mxf = __bfloat1622float2(mx2);
+                    const float new_max = fmaxf(run_max, fmaxf(mxf.x, mxf.y));
+                    const float nm2 = new_max * 1.4426950408889634f;
+                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {
+                        const float2 f = unpack_bf16x2(pk[j]), g = unpack_bf16x2(pk[j + 1]);
+                        s0 += exp2f(fmaf(f.x, 1.4426950408889634f, -nm2));
+                        s1 += exp2f(fmaf(f.y, 1.4426950408889634f, -nm2));
+                        s2 += exp2f(fmaf(g.x, 1.4426950408889634f, -nm2));
+                        s3 += exp2f(fmaf(g.y, 1.4426950408889634f, -nm2));
+                    }
+                    run_sum = run_sum * exp2f(fmaf(run_max, 1.4426950408889634f, -nm2)) + ((s0 + s1) + (s2 + s3));
+                    run_max = new_max;
+                } else {
+                    float cmax = -INFINITY;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         float2 f = unpack_bf16x2(pk[j]);
-                        if (nc0 + 2 * j < p.N) s += __expf(f.x - new_max);
-                        if (nc0 + 2 * j + 1 < p.N) s += __expf(f.y - new_max);
+                        if (nc0 + 2 * j < p.N) cmax = fmaxf(cmax, f.x);
+                        if (nc0 + 2 * j + 1 < p.N) cmax = fmaxf(cmax, f.y);
                     }
-                    run_sum = run_sum * __expf(run_max - new_max) + s;
-                    run_max = new_max;
+                    const float new_max = fmaxf(run_max, cmax);
+                    if (new_max > -INFINITY) {
+                        float s = 0.f;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            float2 f = unpack_bf16x2(pk[j]);
+                            if (nc0 + 2 * j < p.N) s += __expf(f.x - new_max);
+                            if (nc0 + 2 * j + 1 < p.N) s += __expf(f.y - new_max);
+                        }
+                        run_sum = run_sum * __expf(run_max - new_max) + s;
+                        run_max = new_max;
+                    }
                 }
             }
-            // ---- stage in swizzled smem, then one thread issues the TMA store
-            if (store_thread) ptx::tma_store_wait_read<1>();  // buffer `buf` (2 stores ago) is drained
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            // ---- stage in swizzled smem, then one thread issues the TMA store.  Buffer `buf` is free: the store that
+            //      read it (two chunks ago) was waited for before the PREVIOUS chunk's barrier, so one barrier per
+            //      chunk is enough.
             const uint32_t sdst = epi_base + buf * EPI_BUF_BYTES + row * 128;
 #pragma unroll
             for (int ch = 0; ch < 8; ++ch) {
@@ -217,6 +247,7 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
                              : "memory");
             }
             ptx::fence_proxy_async_smem();
+            if (store_thread) ptx::tma_store_wait_read<0>();  // the previous store has left the OTHER buffer
             asm volatile("bar.sync 1, 128;" ::: "memory");
             if (store_thread) {
                 if (nc0 < p.N) ptx::tma_store_2d(tmC, epi_base + buf * EPI_BUF_BYTES, nc0, m0);

@@ -264,7 +264,9 @@ __device__ __forceinline__ uint32_t mapa(uint32_t local_addr, uint32_t rank) {
     return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    // default semantics (.release at CTA scope), like CUTLASS' ClusterBarrier::arrive: the explicit .release.cluster
+    // form compiles to MEMBAR.ALL.GPU + ERRBAR, which showed up as 13% of the epilogue warps' stall samples
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load issued by either CTA of a pair: data lands in THIS CTA's smem, the bytes are credited to the
 // LEADER CTA's mbarrier (same offset, peer bit cleared)
