@@ -31,7 +31,7 @@ using gemm::EPI_BUF_BYTES;
 constexpr int BM = 128;
 constexpr int BK = 64;               // 64 bf16 = 128 bytes = one swizzle row
 constexpr int A_BYTES = BM * BK * 2; // 16 KiB
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;   // TMA warp, MMA warp, 2 groups of 4 epilogue warps (BN = 64 uses one group)
 
 template <int BN> struct Cfg {
     static constexpr int B_BYTES = BN * BK * 2;
@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const Params p) {
     using C = Cfg<BN>;
+    constexpr int NG = BN >= 128 ? 2 : 1;   // epilogue warp groups
     extern __shared__ uint8_t smem_raw[];
     // 128B-swizzled tiles need 1024-byte alignment
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -74,7 +75,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(tfull_bar(s), 1);
-            ptx::mbar_init(tempty_bar(s), 4);  // one arrive per epilogue warp
+            ptx::mbar_init(tempty_bar(s), 4 * NG);  // one arrive per epilogue warp
         }
         ptx::fence_mbar_init();
     }
@@ -165,20 +166,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
-    } else {
-        // ------------------------------------------------------------------ epilogue (warps 2..5)
+    } else if (warp < 2 + 4 * NG) {
+        // ------------------------------------------------------------------ epilogue (warps 2..5 and, for BN >= 128, 6..9)
         const int q = warp & 3;                 // TMEM lane quarter this warp may access
         const int row = q * 32 + lane;          // row inside the 128-row tile
-        const bool store_thread = (threadIdx.x == 64);
+        const int grp = (warp - 2) >> 2;        // epilogue group: takes the 64-column chunks grp, grp + NG, ...
+        const bool store_thread = (threadIdx.x == 64 + 128 * grp);
         int acc = 0;
         uint32_t acc_phase = 0;
-        int buf = 0;
+        int buf = NG == 2 ? grp : 0;
         const int et = (int)threadIdx.x - 64;
         auto n0_of = [&](int u) { return ((u % ntiles) / p.num_m) * BN; };
         float bias_pf[(BN + 127) / 128];
 #pragma unroll
         for (int i = 0; i < (BN + 127) / 128; ++i) {
-            const int j = et + 128 * i;
+            const int j = et + 128 * NG * i;
             bias_pf[i] = (!OUT_F32 && p.bias != nullptr && (int)blockIdx.x < nunits && j < BN && n0_of(blockIdx.x) + j < p.N)
                              ? __ldg(p.bias + n0_of(blockIdx.x) + j) : 0.f;
         }
@@ -189,8 +191,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const int n0_next = (u + (int)gridDim.x < nunits) ? n0_of(u + gridDim.x) : -1;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
             const uint32_t te = tempty_bar(acc);
-            gemm::epilogue_tile<BN, OUT_F32>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base, buf,
-                                             store_thread, s_bias, et, bias_pf, n0_next, [te]() { ptx::mbar_arrive(te); });
+            gemm::epilogue_tile<BN, OUT_F32, NG>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base,
+                                                 buf, store_thread, s_bias, et, bias_pf, n0_next, grp,
+                                                 [te]() { ptx::mbar_arrive(te); });
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (!OUT_F32 && store_thread) ptx::tma_store_wait_all<0>();

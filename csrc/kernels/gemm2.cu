@@ -25,7 +25,7 @@ using gemm::AgParams;
 using gemm::EPI_BUF_BYTES;
 constexpr int BK = 64;
 constexpr int A_BYTES = 128 * BK * 2;   // this CTA's 128 rows of A
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 192;       // TMA warp, MMA warp, 4 epilogue warps; + 4 more epilogue warps (or the 4 gather warps of the AG variant)
 
 template <int BN> struct Cfg2 {
     static constexpr int B_BYTES = (BN / 2) * BK * 2;          // this CTA's half of the B tile
@@ -47,10 +47,11 @@ __device__ __forceinline__ void st_release_gpu(int* p, int v) {
 // AG = true: 4 extra warps (6..9) pull the remote chunks of the layer's weights over NVLink into the local
 // buffer while the tiles whose weights are already local run; the TMA producer waits per chunk.
 template <int BN, bool A_MN, bool B_MN, bool OUT_F32, bool AG>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(AG ? NUM_THREADS + 128 : NUM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS + 128, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmC, const Params p, const AgParams ag) {
     using C = Cfg2<BN>;
+    constexpr int NG = AG ? 1 : 2;          // epilogue warp groups (the AG variant's warps 6..9 gather weights instead)
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t epi_base = smem_base + C::STAGES * C::STAGE_BYTES;
@@ -79,7 +80,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         }
         for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(tfull_bar(s), 1);     // multicast commit
-            ptx::mbar_init(tempty_bar(s), 8);    // 4 epilogue warps x 2 CTAs (used in the leader only)
+            ptx::mbar_init(tempty_bar(s), 8 * NG);   // epilogue warps x 2 CTAs (used in the leader only)
         }
         ptx::fence_mbar_init();
     }
@@ -186,20 +187,21 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
-    } else if (warp < 6) {
-        // ------------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
+    } else if (warp < 2 + 4 * NG) {
+        // ------------------------------------------------------------------ epilogue (warps 2..5 [+ 6..9], both CTAs)
         const int q = warp & 3;
         const int row = q * 32 + lane;
-        const bool store_thread = (threadIdx.x == 64);
+        const int grp = (warp - 2) >> 2;        // epilogue group: takes the 64-column chunks grp, grp + NG, ...
+        const bool store_thread = (threadIdx.x == 64 + 128 * grp);
         int acc = 0;
         uint32_t acc_phase = 0;
-        int buf = 0;
+        int buf = NG == 2 ? grp : 0;
         const int et = (int)threadIdx.x - 64;
         auto n0_of = [&](int u) { return ((((u % ntiles) / p.num_m) + p.n_shift) % p.num_n) * BN; };
         float bias_pf[(BN + 127) / 128];
 #pragma unroll
         for (int i = 0; i < (BN + 127) / 128; ++i) {
-            const int j = et + 128 * i;
+            const int j = et + 128 * NG * i;
             bias_pf[i] = (!OUT_F32 && p.bias != nullptr && pair < nunits && j < BN && n0_of(pair) + j < p.N)
                              ? __ldg(p.bias + n0_of(pair) + j) : 0.f;
         }
@@ -210,9 +212,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             const int n0_next = (u + npairs < nunits) ? n0_of(u + npairs) : -1;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
             const uint32_t te = ptx::mapa(tempty_bar(acc), 0);   // the leader's accumulator-empty barrier
-            gemm::epilogue_tile<BN, OUT_F32>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base,
-                                             buf, store_thread, s_bias, et, bias_pf, n0_next,
-                                             [te]() { ptx::mbar_arrive_cluster(te); });
+            gemm::epilogue_tile<BN, OUT_F32, NG>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base,
+                                                 buf, store_thread, s_bias, et, bias_pf, n0_next, grp,
+                                                 [te]() { ptx::mbar_arrive_cluster(te); });
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (!OUT_F32 && store_thread) ptx::tma_store_wait_all<0>();
@@ -272,7 +274,7 @@ int launch2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
     }
     AgParams none;
     memset(&none, 0, sizeof(none));
-    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(AG ? NUM_THREADS + 128 : NUM_THREADS), Cfg2<BN>::SMEM_BYTES, st, tA, tB, tC, p, ag ? *ag : none));
+    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NUM_THREADS + 128), Cfg2<BN>::SMEM_BYTES, st, tA, tB, tC, p, ag ? *ag : none));
     return 0;
 }
 

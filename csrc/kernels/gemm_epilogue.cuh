@@ -1,7 +1,10 @@
 // Shared epilogue of the tcgen05 GEMM kernels (1-CTA gemm.cu and 2-CTA gemm2.cu): one 128-row x BN-column
 // accumulator tile, TMEM -> registers -> (bf16: bias / ReLU / ReLU-mask / softmax statistics -> swizzled smem ->
-// TMA store) or (fp32: store / accumulate / atomic add).  Called by the 4 epilogue warps (128 threads,
-// thread <-> accumulator row); `arrive_tempty()` hands the TMEM stage back to the MMA issuer.
+// TMA store) or (fp32: store / accumulate / atomic add).  Called by NG groups of 4 epilogue warps (128 threads
+// per group, thread <-> accumulator row); group g takes the 64-column chunks g, g + NG, ... of the tile, so with
+// NG = 2 the epilogue of a tile takes half as long (one warp per scheduler cannot hide its own instruction
+// latencies: with 4 warps the bias/ReLU/sign-bit and CE-statistics epilogues of the K = 768 GEMMs were longer than
+// their main loops).  `arrive_tempty()` hands the TMEM stage back to the MMA issuer (once per warp).
 #pragma once
 #include <cuda.h>
 
@@ -56,36 +59,45 @@ struct AgParams {
 // thread's lane quarter at the accumulator stage's first column; m0: first global row of this CTA's 128 rows.
 // bias_pf: this thread's share of the CURRENT tile's bias slice, loaded one tile ahead (n0_next: first column of the
 // next tile of this CTA, < 0 if none) so the global-load latency never sits in front of a tile's epilogue.
-template <int BN, bool OUT_F32, class ArriveFn>
+template <int BN, bool OUT_F32, int NG, class ArriveFn>
 __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap* tmC, uint32_t tfull_bar, uint32_t acc_phase,
                                               uint32_t taddr, int m0, int n0, int n_blk, int row, int lane,
                                               uint32_t epi_base, int& buf, bool store_thread, float* s_bias, int et,
-                                              float (&bias_pf)[(BN + 127) / 128], int n0_next, ArriveFn arrive_tempty) {
+                                              float (&bias_pf)[(BN + 127) / 128], int n0_next, int grp,
+                                              ArriveFn arrive_tempty) {
+    // et: thread index among ALL epilogue threads (0 .. 128*NG-1); grp = et / 128; buf: staging buffer (NG = 1: the two
+    // buffers alternate; NG = 2: group g owns buffer g)
+    constexpr int NCH = BN / 64;
+    constexpr int NTE = 128 * NG;                        // epilogue threads
+    constexpr int NPF = (BN + 127) / 128;
     const int m = m0 + row;
+    const uint32_t bar_id = 1 + grp;
     if (!OUT_F32 && p.bias != nullptr) {
         // stage this tile's bias slice in smem while the MMAs are still running
-        asm volatile("bar.sync 1, 128;" ::: "memory");          // previous tile's readers are done
+        asm volatile("bar.sync 3, %0;" ::"n"(NTE) : "memory");          // previous tile's readers are done
 #pragma unroll
-        for (int i = 0; i < (BN + 127) / 128; ++i) {
-            const int j = et + 128 * i;
-            if (j < BN) s_bias[j] = bias_pf[i];
-            bias_pf[i] = (n0_next >= 0 && j < BN && n0_next + j < p.N) ? __ldg(p.bias + n0_next + j) : 0.f;
+        for (int i = 0; i < NPF; ++i) {
+            const int j = et + NTE * i;
+            if (i * NTE < BN) {
+                if (j < BN) s_bias[j] = bias_pf[i];
+                bias_pf[i] = (n0_next >= 0 && j < BN && n0_next + j < p.N) ? __ldg(p.bias + n0_next + j) : 0.f;
+            }
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 3, %0;" ::"n"(NTE) : "memory");
     }
     // ReLU sign bits of this row for the whole tile: loaded while the MMAs are still running
     const int ld_bits = (p.N + 63) >> 6;
-    unsigned long long mbits[BN / 64];
+    unsigned long long mbits[NCH];
     if (!OUT_F32 && p.relu_bits != nullptr) {
 #pragma unroll
-        for (int c = 0; c < BN / 64; ++c)
+        for (int c = 0; c < NCH; ++c)
             mbits[c] = (m < p.M && (n0 >> 6) + c < ld_bits) ? __ldg(p.relu_bits + (size_t)m * ld_bits + (n0 >> 6) + c) : 0ull;
     }
     ptx::mbar_wait(tfull_bar, acc_phase);
     ptx::tc_fence_after();
     float run_max = -INFINITY, run_sum = 0.f;
 #pragma unroll 1
-    for (int c = 0; c < BN / 64; ++c) {
+    for (int c = grp; c < NCH; c += NG) {
         const int nc0 = n0 + c * 64;
         uint4 mk4[8];
         if (!OUT_F32 && p.mask != nullptr && m < p.M) {
@@ -103,8 +115,8 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
             ptx::tmem_ld_32x32(taddr + c * 64 + 32, r1);
             ptx::tmem_ld_wait();
         }
-        if (c == BN / 64 - 1) {
-            // all TMEM reads of this accumulator stage are done: hand it back to the MMA warp
+        if (c + NG >= NCH) {
+            // all TMEM reads of this warp for this accumulator stage are done: hand it back to the MMA warp
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) arrive_tempty();
@@ -165,7 +177,11 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
                 }
             }
             if (p.relu_bits != nullptr) {
-                const uint32_t lo = (uint32_t)mbits[c], hi = (uint32_t)(mbits[c] >> 32);
+                unsigned long long mb = 0ull;          // register select: a dynamic index would put mbits[] in local memory
+#pragma unroll
+                for (int i = 0; i < NCH; ++i)
+                    if (i == c) mb = mbits[i];
+                const uint32_t lo = (uint32_t)mb, hi = (uint32_t)(mb >> 32);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     if (!(lo & (1u << j))) r[j] = 0u;
@@ -179,14 +195,16 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
                 pk[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
             if (p.relu_bits_out != nullptr) {
                 // sign bits of the bf16-ROUNDED outputs (what the activation tensor holds); after the ReLU they are >= 0
-                uint32_t lo = 0u, hi = 0u;
+                // four independent partial words per half: one OR chain of 32 would serialise the lone epilogue warp
+                uint32_t lw[4] = {0u, 0u, 0u, 0u}, hw[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    if (pk[j] & 0x00007fffu) lo |= 1u << (2 * j);
-                    if (pk[j] & 0x7fff0000u) lo |= 1u << (2 * j + 1);
-                    if (pk[16 + j] & 0x00007fffu) hi |= 1u << (2 * j);
-                    if (pk[16 + j] & 0x7fff0000u) hi |= 1u << (2 * j + 1);
+                    if (pk[j] & 0x00007fffu) lw[j & 3] |= 1u << (2 * j);
+                    if (pk[j] & 0x7fff0000u) lw[j & 3] |= 1u << (2 * j + 1);
+                    if (pk[16 + j] & 0x00007fffu) hw[j & 3] |= 1u << (2 * j);
+                    if (pk[16 + j] & 0x7fff0000u) hw[j & 3] |= 1u << (2 * j + 1);
                 }
+                const uint32_t lo = (lw[0] | lw[1]) | (lw[2] | lw[3]), hi = (hw[0] | hw[1]) | (hw[2] | hw[3]);
                 if (m < p.M && nc0 < p.N)
                     p.relu_bits_out[(size_t)m * ld_bits + (nc0 >> 6)] = ((unsigned long long)hi << 32) | lo;
             }
@@ -238,6 +256,11 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
             // ---- stage in swizzled smem, then one thread issues the TMA store.  Buffer `buf` is free: the store that
             //      read it (two chunks ago) was waited for before the PREVIOUS chunk's barrier, so one barrier per
             //      chunk is enough.
+            if (NG == 2) {
+                // this group's single buffer: its previous store must have left it
+                if (store_thread) ptx::tma_store_wait_read<0>();
+                asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+            }
             const uint32_t sdst = epi_base + buf * EPI_BUF_BYTES + row * 128;
 #pragma unroll
             for (int ch = 0; ch < 8; ++ch) {
@@ -247,17 +270,18 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
                              : "memory");
             }
             ptx::fence_proxy_async_smem();
-            if (store_thread) ptx::tma_store_wait_read<0>();  // the previous store has left the OTHER buffer
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (NG == 1 && store_thread) ptx::tma_store_wait_read<0>();  // the previous store has left the OTHER buffer
+            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             if (store_thread) {
                 if (nc0 < p.N) ptx::tma_store_2d(tmC, epi_base + buf * EPI_BUF_BYTES, nc0, m0);
                 ptx::tma_store_commit();
             }
-            buf ^= 1;
+            if (NG == 1) buf ^= 1;
         }
     }
-    if (!OUT_F32 && p.stats != nullptr && m < p.M)
-        p.stats[(size_t)n_blk * p.M + m] = make_float2(run_max, run_sum);
+    // one (max, sum exp) entry per row, n-tile and epilogue group: the CE kernels merge any number of entries per row
+    if (!OUT_F32 && p.stats != nullptr && m < p.M && grp < NCH)
+        p.stats[((size_t)n_blk * NG + grp) * p.M + m] = make_float2(run_max, run_sum);
 }
 
 }  // namespace gemm

@@ -62,8 +62,12 @@ int b200_ln_bwd_static(const void* dy, const float* x, const float* mean, const 
  * C[M,N] = alpha * opA * opB^T.   a_mn = 0: A is [M,K] (K contiguous); 1: A is [K,M].
  *                                  b_mn = 0: B is [N,K] (K contiguous); 1: B is [K,N].
  * out_f32 = 0: C bf16 via TMA store, epilogue = (+bias[N]) (ReLU) (* (mask[M,N] > 0)), and if
- *              `stats` != null per-(n-tile,row) float2 (max, sum exp) -> stats[n_tile * M + row]
- *              with n-tile width b200_gemm_pick_bn() or bn_override.
+ *              `stats` != null: float2 (max, sum exp) of the bf16 outputs per row, n-tile (width
+ *              b200_gemm_pick_bn() or bn_override) and epilogue warp group g (g < 2 for tiles of 128 or 256 columns,
+ *              1 group for 64) -> stats[(n_tile * groups + g) * M + row]; consumers merge any number of entries.
+ *              `relu_bits_out` / `relu_bits`: one 64-bit word per row and 64 columns, [M][ceil(N/64)]; the GEMM
+ *              that applies the ReLU writes bit j = (output column 64 w + j > 0), the matching dgrad GEMM zeroes
+ *              the outputs whose bit is clear (cheaper than re-reading the activations as `mask`).
  * out_f32 = 1: C fp32, f32_mode 0 store / 1 accumulate / 2 atomic add (enables split-K;
  *              split_k = 0 picks automatically, C must then hold the running sum). */
 int b200_gemm_pick_bn(int M, int N, int K, int out_f32);

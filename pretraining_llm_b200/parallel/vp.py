@@ -53,7 +53,7 @@ class VocabParallelHead:
         self.n_local = max(0, min(V, self.v0 + self.Vs) - self.v0)
         assert self.n_local > 0, "vocabulary too small for this many ranks"
         self.ldl = self.Vs
-        self.nt = (self.Vs + 255) // 256
+        self.nt = 2 * ((self.Vs + 255) // 256)      # CE statistics entries per row (256-column tile x epilogue group)
         self.sig = SymmBuffer(4 * W * 4, self.rank, W, eng.device)
         self.ws: Dict[int, _VpWorkspace] = {}
         d = lay.d

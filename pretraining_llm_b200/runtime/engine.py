@@ -60,7 +60,7 @@ class Workspace:
         self.hf = e(M, d)
         self.Vp = (V + 7) // 8 * 8
         self.logits = e(M, self.Vp)
-        self.nt = (V + 255) // 256
+        self.nt = 2 * ((V + 255) // 256)            # CE statistics entries per row: one per 256-column tile and epilogue group
         self.ce_stats = e(self.nt, M, 2, dt=F32)
         self.ce_lse = e(M, dt=F32)
         self.loss_rows = e(M, dt=F32)

@@ -155,7 +155,7 @@ def test_gemm_stats(ops):
     bias = torch.randn(V, device="cuda") * 0.1
     Vp = (V + 7) // 8 * 8
     logits = torch.empty(M, Vp, device="cuda", dtype=BF16)
-    nt = (V + 255) // 256
+    nt = 2 * ((V + 255) // 256)          # one entry per 256-column tile and epilogue warp group
     stats = torch.zeros(nt, M, 2, device="cuda")
     ops.gemm(h, w, out=logits[:, :V], bias=bias, stats=stats, bn=256)
     lse = torch.empty(M, device="cuda")

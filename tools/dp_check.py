@@ -73,7 +73,11 @@ def main():
         print(f"world {W}: max|dW| {dw:.3e}  max|dm| {dm:.3e}  max|dv| {dv:.3e}  replicas_identical {ok}  "
               f"losses {[round(float(v), 4) for v in mean_loss]}")
         assert ok, "bf16 weight replicas differ between ranks"
-        assert dw < 5e-3 and dm < 5e-3, (dw, dm)
+        # The moments are linear in the gradients and must agree tightly.  A weight can legitimately differ by up to
+        # ~lr per step where Adam divides a rounding-level gradient by a rounding-level sqrt(v) (sign flips between two
+        # summation orders), so the weights are held to a bound on the MEAN difference plus the hard per-step cap.
+        dw_mean = (eng.flat - o.flat).abs().mean().item()
+        assert dm < 1e-3 and dw_mean < 0.02 * LR * STEPS and dw <= 1.5 * LR * STEPS, (dw, dw_mean, dm)
         print("DP_CHECK_OK")
     ctx.shutdown()
 
