@@ -191,8 +191,18 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
     memset(&S, 0, sizeof(S));
     S.n = n_slots;
     for (int k = 0; k < n_slots; ++k) { S.end[k] = h_slot_end[k]; S.fp32[k] = h_slot_fp32[k]; }
+    // CTA size: 512 threads measured best (B200_DP_THREADS sweeps it).  Smaller CTAs (128 threads = 7.4K registers) can
+    // share an SM with the backward's GEMM / attention CTAs, which 512 x 58 registers cannot, but the step got SLOWER
+    // (2 GPUs: 18.7 ms at 128 threads vs 17.0 ms at 512): what is exposed is the last bucket (embeddings), whose
+    // duration is set by the bytes the kernel keeps in flight, not by co-residency with compute.
+    static int threads = 0;
+    if (threads == 0) {
+        const char* e = getenv("B200_DP_THREADS");
+        threads = e ? atoi(e) : 512;
+        if (threads < 32 || threads > 512 || threads % 32) threads = 512;
+    }
 #define DP_LAUNCH(W_)                                                                                            \
-    B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
+    B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
                                                      (unsigned int*)cta_counter, err, zero_mode))
     switch (world) {
         case 1: DP_LAUNCH(1); break;
