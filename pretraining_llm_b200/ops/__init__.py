@@ -81,14 +81,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     fn = L.b200_gemm_2cta if two_cta else L.b200_gemm
     if two_cta and bn == 0:
         bn = 256
-    if two_cta and out_f32 and split_k == 0 and f32_mode in (0, 1):
-        # small weight-gradient outputs with a huge K (tokens): too few 256x256 tiles for the 74 CTA pairs ->
-        # split K in two and combine with fp32 RED (measured best on B200: tools/sweep_wgrad.py)
+    if two_cta and out_f32 and split_k == 0 and f32_mode in (0, 1) and bn == 256:
+        # small weight-gradient outputs with a huge K (tokens): too few 256x256 tiles for the 74 CTA pairs.  256x128
+        # tiles fill the machine without split-K, i.e. without a zero-fill launch and without fp32 atomics (deterministic
+        # gradients); measured equal to split-K = 2 + fill on B200 (tools/sweep_wgrad.py).
         tiles = ((M + 255) // 256) * ((N + bn - 1) // bn)
         if tiles <= 48 and K >= 2048:
-            if f32_mode == 0:
-                out.zero_()
-            f32_mode, split_k = 2, 2
+            bn = 128
     rc = fn(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
             int(a_mn), int(b_mn), int(out_f32), f32_mode, float(alpha), _p(bias), int(relu),
             _p(mask), 0 if mask is None else mask.stride(0), _p(stats), _p(relu_bits_out), _p(relu_bits), bn, split_k,
