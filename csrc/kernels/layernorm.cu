@@ -125,8 +125,15 @@ __global__ void __launch_bounds__(256, 2)
     for (int row = blockIdx.x * G + group; row < M; row += gridDim.x * G) {
         const size_t base4 = (size_t)row * D4;
         const float mu = mean[row], rs = rstd[row];
-        float4 xh[VPL], gd[VPL];
+        float4 xh[VPL], gd[VPL], pin[VPL];
         float s1 = 0.f, s2 = 0.f;
+        // the incoming residual gradient is only needed after the row reduction, but loading it HERE keeps it in the
+        // same memory round trip as x and dy (it was a second, serialised round trip per row: 71% -> of the HBM floor)
+        if (dx_in != nullptr) {
+#pragma unroll
+            for (int i = 0; i < VPL; ++i)
+                pin[i] = reinterpret_cast<const float4*>(dx_in)[base4 + wir * 32 + lane + i * 32 * WPR];  // may alias dx_out
+        }
 #pragma unroll
         for (int i = 0; i < VPL; ++i) {
             const int c = wir * 32 + lane + i * 32 * WPR;
@@ -163,7 +170,7 @@ __global__ void __launch_bounds__(256, 2)
             r.z = rs * (gd[i].z - c1 - xh[i].z * c2);
             r.w = rs * (gd[i].w - c1 - xh[i].w * c2);
             if (dx_in != nullptr) {
-                float4 p = reinterpret_cast<const float4*>(dx_in)[base4 + c];  // may alias dx_out
+                const float4 p = pin[i];
                 if (COLSUM) { acc_c[i].x += p.x; acc_c[i].y += p.y; acc_c[i].z += p.z; acc_c[i].w += p.w; }
                 r.x += p.x; r.y += p.y; r.z += p.z; r.w += p.w;
             }
