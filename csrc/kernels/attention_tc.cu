@@ -2,16 +2,19 @@
 //
 // One CTA = one 128-query tile of one (batch, head).  Per 128-key tile j <= diagonal:
 //     S  = Q K_j^T          tcgen05.mma  M=128 N=128 K=hs   (Q, K tiles in smem via 3-D TMA)  -> TMEM
-//     P  = exp2(S*c - m)    128 softmax threads, one query row each, S read with tcgen05.ld;
-//                           P is rounded to bf16 and written to swizzled smem (like the reference,
-//                           which casts probabilities to bf16 before attn @ v)
-//     O += P V_j            tcgen05.mma  M=128 N=hs  K=128  (V is the MN-major B operand)     -> TMEM
+//     P  = exp2(S*c - m)    128 softmax threads, one query row each.  The row's 128 scores are read from
+//                           TMEM ONCE (tcgen05.ld) and kept in registers; P is rounded to bf16 (like the
+//                           reference, which casts probabilities to bf16 before attn @ v) and written back
+//                           OVER the scores in TMEM, two values per 32-bit column
+//     O += P V_j            tcgen05.mma  M=128 N=hs  K=128  A = P from TENSOR MEMORY (TS form), B = V read
+//                           MN-major from smem                                                  -> TMEM
 // O stays in TMEM for the whole row of tiles.  The running max is LAZY: it only moves (and O is
 // only rescaled, with tcgen05.ld/st) when the tile maximum exceeds it by more than 2^8, so most
 // tiles skip the correction entirely; the final O / l uses the same max, so the result is exact.
-// Warp roles: warp 0 TMA producer (Q once, K/V double-buffered), warp 1 MMA issuer, warps 2-5
-// softmax + epilogue.  hs=64 runs two CTAs per SM (256 TMEM columns each) so one CTA's
-// exponentials overlap the other's MMAs; hs=128 double-buffers S instead.
+// Warp roles: warp 0 TMA producer (Q once, K/V double-buffered), warp 1 MMA issuer (whole warp converged,
+// one elected lane per instruction, see ptx.cuh), warps 2-5 softmax + epilogue.  hs=64 runs two CTAs per SM
+// (256 TMEM columns each) so one CTA's exponentials overlap the other's MMAs; hs=128 double-buffers S instead.
+// CTAs are ordered heaviest query tile first (1-D grid, all (b, h) of the last tile, then the one before, ...).
 //
 // Replaces reference src/models/attention.py:45-58,95 (see attention.cu for the layout contract).
 #include <cuda.h>

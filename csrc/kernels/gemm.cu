@@ -3,14 +3,16 @@
 //   * operands bf16, accumulation fp32 in TMEM (two accumulator stages of BN columns, so the
 //     epilogue of tile i overlaps the MMAs of tile i+1);
 //   * A/B tiles staged in shared memory by TMA (128-byte swizzle) through a STAGES-deep mbarrier
-//     ring; one elected thread issues tcgen05.mma (M=128, N=BN, K=16 per instruction);
+//     ring; the MMA warp runs converged and one elected lane issues tcgen05.mma (M=128, N=BN, K=16 per
+//     instruction) with warp-uniform operands (see ptx.cuh, `*_w` wrappers);
 //   * either operand may be K-major ([rows, K] row-major - the forward "x @ W^T" layout) or
 //     MN-major ([K, rows] row-major), which is what dgrad (dY @ W) and wgrad (dY^T @ X) need
 //     without any transposed copies of activations or weights;
-//   * warp roles: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue (one TMEM lane
-//     quarter each);
+//   * warp roles: warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 and 6-9 two epilogue groups (one TMEM
+//     lane quarter per warp, the groups split a tile's 64-column chunks; BN = 64 uses one group);
 //   * epilogues: bf16 out through swizzled smem + TMA store, with optional per-column bias, ReLU,
-//     ReLU-backward mask and per-(row, n-tile) softmax statistics for the fused LM-head/CE path;
+//     ReLU sign bits out / sign-bit mask in (ReLU backward), and per-(row, n-tile, group) softmax statistics for
+//     the fused LM-head/CE path;
 //     or fp32 out (plain / accumulate / atomic for split-K) for weight gradients.
 //
 // Replaces every cuBLAS/cuBLASLt call the reference makes through nn.Linear and autograd
