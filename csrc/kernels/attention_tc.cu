@@ -34,15 +34,24 @@ struct MaskOn { static constexpr bool value = true; };
 struct MaskOff { static constexpr bool value = false; };
 constexpr int NTHREADS_BWD = 64 + 32 * BWD_EW_WARPS;   // TMA warp + MMA warp + elementwise warps
 
+// Optional forward timeline (tools/attn_trace.cu, -DATTN_TRACE): CTA 0, clock64() at the hand-offs.  Compiled out otherwise.
+#ifdef ATTN_TRACE
+__device__ long long g_attn_trace_fwd[2][64][8];   // [role: 0 MMA warp, 1 softmax warp 2][tile][event]
+#define TRACEF(role, n, k) do { if (blockIdx.x == 0 && (n) < 64) g_attn_trace_fwd[role][n][k] = clock64(); } while (0)
+#else
+#define TRACEF(role, n, k) do { } while (0)
+#endif
+
 template <int HD> struct ACfg {
     static constexpr int NSUB = HD / 64;                 // sub-tiles per Q / K / V tile
     static constexpr int TILE = NSUB * SUB;
     static constexpr int S_BUFS = HD == 64 ? 1 : 2;
+    static constexpr int KV = HD == 64 ? 2 : 3;          // K / V ring depth (a cold K/V tile takes ~2500 clk to arrive)
     static constexpr int TMEM_COLS = HD == 64 ? 256 : 512;
     static constexpr int O_COL = 128 * S_BUFS;
     // smem: Q | K[2] | V[2] | barriers
     // + barriers (256 B) + alignment slack (768 B: lets two hs=64 CTAs share one SM's 227 KB)
-    static constexpr int USED = TILE + 2 * TILE + 2 * TILE + 256;
+    static constexpr int USED = TILE + KV * TILE + KV * TILE + 256;
     static constexpr int SMEM = USED + 768;
 };
 
@@ -55,17 +64,17 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t sQ = base;
     const uint32_t sK = sQ + C::TILE;
-    const uint32_t sV = sK + 2 * C::TILE;
-    const uint32_t bars = sV + 2 * C::TILE;
+    const uint32_t sV = sK + C::KV * C::TILE;
+    const uint32_t bars = sV + C::KV * C::TILE;
     const uint32_t q_full = bars;
-    auto k_full = [&](int s) { return bars + 8u * (1 + s); };
-    auto k_empty = [&](int s) { return bars + 8u * (3 + s); };
-    auto v_full = [&](int s) { return bars + 8u * (5 + s); };
-    auto v_empty = [&](int s) { return bars + 8u * (7 + s); };
-    auto s_full = [&](int s) { return bars + 8u * (9 + s); };
-    const uint32_t p_full = bars + 8u * 13;
-    const uint32_t pv_done = bars + 8u * 14;
-    const uint32_t tmem_slot = bars + 8u * 15;
+    auto k_full = [&](int s) { return bars + 8u * (1 + s); };            // KV (<= 3) each
+    auto k_empty = [&](int s) { return bars + 8u * (4 + s); };
+    auto v_full = [&](int s) { return bars + 8u * (7 + s); };
+    auto v_empty = [&](int s) { return bars + 8u * (10 + s); };
+    auto s_full = [&](int s) { return bars + 8u * (13 + s); };
+    auto p_full = [&](int s) { return bars + 8u * (15 + s); };           // P_j ready: p_full(j & 1), phase j >> 1
+    auto pv_done = [&](int s) { return bars + 8u * (17 + s); };          // PV_j commits to pv_done(j & 1): phase j >> 1
+    const uint32_t tmem_slot = bars + 8u * 19;
     uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
     if (base - ptx::smem_u32(smem_raw) > 768u) __trap();   // dynamic smem window less aligned than assumed
 
@@ -84,13 +93,17 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     }
     if (warp == 1 && lane == 0) {
         ptx::mbar_init(q_full, 1);
-        for (int s = 0; s < 2; ++s) {
+        for (int s = 0; s < C::KV; ++s) {
             ptx::mbar_init(k_full(s), 1); ptx::mbar_init(k_empty(s), 1);
             ptx::mbar_init(v_full(s), 1); ptx::mbar_init(v_empty(s), 1);
+        }
+        for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(s_full(s), 1);
         }
-        ptx::mbar_init(p_full, 4);
-        ptx::mbar_init(pv_done, 1);
+        ptx::mbar_init(p_full(0), 4);
+        ptx::mbar_init(p_full(1), 4);
+        ptx::mbar_init(pv_done(0), 1);
+        ptx::mbar_init(pv_done(1), 1);
         ptx::fence_mbar_init();
     }
     if (warp == 2) {
@@ -111,8 +124,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
 #pragma unroll
             for (int c = 0; c < C::NSUB; ++c) ptx::tma_load_3d_w(sQ + c * SUB, &tmQKV, q_full, h * HD + c * 64, q0, b);
             for (int j = 0; j < ntiles; ++j) {
-                const int st = j & 1;
-                const uint32_t ph = ((j >> 1) & 1) ^ 1;
+                const int st = j % C::KV;
+                const uint32_t ph = ((j / C::KV) & 1) ^ 1;
                 ptx::mbar_wait(k_empty(st), ph);
                 ptx::mbar_arrive_expect_tx_w(k_full(st), C::TILE);
 #pragma unroll
@@ -134,9 +147,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             // S buffer sb is rewritten by S_{j} only after PV_{j - S_BUFS} (which read the bf16 P aliased onto it) was
             // issued by this same warp: tcgen05.mma executes in issue order, so no barrier is needed for that.
             auto issue_s = [&](int j) {
-                const int st = j & 1, sb = j % C::S_BUFS;
-                ptx::mbar_wait(k_full(st), (j >> 1) & 1);
+                const int st = j % C::KV, sb = j % C::S_BUFS;
+                ptx::mbar_wait(k_full(st), (j / C::KV) & 1);
                 ptx::tc_fence_after();
+                TRACEF(0, j, 0);
 #pragma unroll
                 for (int kk = 0; kk < HD / 16; ++kk) {
                     const uint64_t ad = ptx::umma_desc(sQ + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
@@ -145,22 +159,26 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 }
                 ptx::mma_commit_w(s_full(sb));
                 ptx::mma_commit_w(k_empty(st));
+                TRACEF(0, j, 1);
             };
             ptx::mbar_wait(q_full, 0);
             issue_s(0);
             for (int j = 0; j < ntiles; ++j) {
-                const int st = j & 1, sb = j % C::S_BUFS;
+                const int st = j % C::KV, sb = j % C::S_BUFS;
                 if (C::S_BUFS == 2 && j + 1 < ntiles) issue_s(j + 1);      // other buffer: overlaps softmax_j
-                ptx::mbar_wait(p_full, j & 1);
-                ptx::mbar_wait(v_full(st), (j >> 1) & 1);
+                ptx::mbar_wait(p_full(j & 1), (j >> 1) & 1);
+                TRACEF(0, j, 2);
+                ptx::mbar_wait(v_full(st), (j / C::KV) & 1);
                 ptx::tc_fence_after();
+                TRACEF(0, j, 3);
 #pragma unroll
                 for (int kk = 0; kk < BN / 16; ++kk) {
                     // A = P [128 q x 128 kv] bf16 in TMEM (8 columns per K=16 slice, aliased onto S); B = V [kv x hs], MN-major
                     const uint64_t bd = ptx::umma_desc(sV + st * C::TILE + kk * 2048, SUB, 1024);
                     ptx::mma_bf16_ts_w(tmem + C::O_COL, tmem + sb * 128 + 8 * kk, bd, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
                 }
-                ptx::mma_commit_w(pv_done);
+                ptx::mma_commit_w(pv_done(j & 1));
+                TRACEF(0, j, 4);
                 ptx::mma_commit_w(v_empty(st));
                 if (C::S_BUFS == 1 && j + 1 < ntiles) issue_s(j + 1);      // same buffer: in order behind PV_j
             }
@@ -174,8 +192,10 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         float m_used = -INFINITY, l = 0.f;
         for (int j = 0; j < ntiles; ++j) {
             const int sb = j % C::S_BUFS;
+            if (threadIdx.x == 64) TRACEF(1, j, 0);
             ptx::mbar_wait(s_full(sb), (j / C::S_BUFS) & 1);
             ptx::tc_fence_after();
+            if (threadIdx.x == 64) TRACEF(1, j, 1);
             const uint32_t ts = tmem + lane_off + sb * 128;
             const bool diag = (j == qt);
             const int k0 = j * BN;
@@ -196,15 +216,19 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
             for (int c = 0; c < 4; ++c)
 #pragma unroll
                 for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+            if (threadIdx.x == 64) TRACEF(1, j, 2);
             const float xmax = mx * scale_log2;
             const bool need = xmax > m_used + 8.f;          // also true on the first tile (m_used = -inf)
             const float m_new = need ? xmax : m_used;
             const float alpha = need ? exp2f(m_used - m_new) : 1.f;
-            // O belongs to PV_{j-1} until it has completed
-            if (j > 0) {
-                ptx::mbar_wait(pv_done, (j - 1) & 1);
+            // O belongs to PV_{j-1} until it has completed - but only a RESCALE touches O, and the lazy maximum makes
+            // that rare: without one the exponentials below overlap PV_{j-1}.  (P_j itself goes into S buffer j % S_BUFS,
+            // whose last reader PV_{j-S_BUFS} is complete once s_full(j) is.)  Two barriers alternate so that a wait
+            // skipped on earlier tiles can never alias a later phase of the same parity.
+            if (j > 0 && __any_sync(0xffffffffu, need)) {
+                ptx::mbar_wait(pv_done((j - 1) & 1), ((j - 1) >> 1) & 1);
                 ptx::tc_fence_after();
-                if (__any_sync(0xffffffffu, need)) {
+                {
 #pragma unroll 1
                     for (int c = 0; c < HD / 32; ++c) {
                         uint32_t o[32];
@@ -216,6 +240,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                     }
                 }
             }
+            if (threadIdx.x == 64) TRACEF(1, j, 3);
             l *= alpha;
             m_used = m_new;
             // ---- probabilities -> bf16 pairs -> back into the first 64 columns of the S buffer (A operand of PV)
@@ -234,13 +259,15 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 ptx::tmem_st_32x16(ts + c * 16, pk);
             }
             l += rs0 + rs1;
+            if (threadIdx.x == 64) TRACEF(1, j, 4);
             ptx::tmem_st_wait();
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(p_full);
+            if (lane == 0) ptx::mbar_arrive(p_full(j & 1));
+            if (threadIdx.x == 64) TRACEF(1, j, 5);
         }
         // ---- epilogue: O / l -> bf16 -> smem (Q's tile is free now) -> TMA store; LSE -> global
-        ptx::mbar_wait(pv_done, (ntiles - 1) & 1);
+        ptx::mbar_wait(pv_done((ntiles - 1) & 1), ((ntiles - 1) >> 1) & 1);
         ptx::tc_fence_after();
         const float inv = l > 0.f ? 1.f / l : 0.f;
 #pragma unroll 1
