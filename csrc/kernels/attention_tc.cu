@@ -308,7 +308,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
 }
 
 template <int HD>
-int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, float scale, cudaStream_t st) {
+int launch_fwd_1tile(const void* qkv, void* out, float* lse, int B, int T, int H, float scale, cudaStream_t st) {
     using C = ACfg<HD>;
     const int d = H * HD;
     CUtensorMap tq, to;
@@ -325,6 +325,291 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, floa
                                 scale * 1.4426950408889634f));
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Forward, two query tiles per CTA ("ping-pong"): the kernel the library launches.
+//
+// One CTA (one per SM) = 256 consecutive queries of one (batch, head) = tiles A and B, which share every K/V tile.
+// Each tile has its own score buffer and O accumulator in TMEM and its own group of 4 softmax warps.  The MMA warp
+// alternates  PV_A(j), S_A(j+1), PV_B(j), S_B(j+1),  so group B runs about half a tile behind group A: while A reads
+// its 64 KB of scores out of TMEM (16 B/clk per lane quarter: 1024 clk) B is in its MUFU.EX2 phase (another 1024 clk),
+// and vice versa - the two phases that bound a tile (profiles/attn_bwd_timeline.md) overlap instead of adding up.
+// Two independent CTAs per SM (the previous hs = 64 layout) start in phase and stay there.
+// ---------------------------------------------------------------------------------------------
+template <int HD> struct A2Cfg {
+    static constexpr int NSUB = HD / 64;
+    static constexpr int TILE = NSUB * SUB;
+    static constexpr int KV = 2;                           // K / V ring depth
+    static constexpr int TMEM_COLS = 512;                  // S_A 0 | S_B 128 | O_A 256 | O_B 256 + HD
+    static constexpr int O_COL = 256;
+    static constexpr int USED = 2 * TILE + 2 * KV * TILE + 256;   // Q_A Q_B | K ring | V ring | barriers
+    static constexpr int SMEM = USED + 1024;
+    static_assert(O_COL + 2 * HD <= 512, "TMEM budget");
+    static_assert(SMEM <= 232448, "smem budget");
+};
+constexpr int NTHREADS_FWD2 = 320;     // TMA warp, MMA warp, 4 softmax warps per query tile
+
+template <int HD>
+__global__ void __launch_bounds__(NTHREADS_FWD2, 1)
+attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
+                    float* __restrict__ lse_out, int T, int H, int HB, int npairs, float scale_log2) {
+    using C = A2Cfg<HD>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    auto sQ = [&](int g) { return base + (uint32_t)g * C::TILE; };
+    const uint32_t sK = base + 2 * C::TILE;
+    const uint32_t sV = sK + C::KV * C::TILE;
+    const uint32_t bars = sV + C::KV * C::TILE;
+    const uint32_t q_full = bars;
+    auto k_full = [&](int s) { return bars + 8u * (1 + s); };
+    auto k_empty = [&](int s) { return bars + 8u * (3 + s); };
+    auto v_full = [&](int s) { return bars + 8u * (5 + s); };
+    auto v_empty = [&](int s) { return bars + 8u * (7 + s); };
+    auto s_full = [&](int g) { return bars + 8u * (9 + g); };      // per query tile, phase = key tile j
+    auto p_full = [&](int g) { return bars + 8u * (11 + g); };
+    auto pv_done = [&](int g) { return bars + 8u * (13 + g); };
+    const uint32_t tmem_slot = bars + 8u * 15;
+    uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
+
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
+    // 1-D grid in longest-processing-time order: ALL (b, h) of the heaviest (last) pair of query tiles first
+    const int rank = (int)blockIdx.x / HB, hb = (int)blockIdx.x - rank * HB;
+    const int pr = npairs - 1 - rank;
+    const int h = hb % H, b = hb / H;
+    const int d_model = H * HD;
+    // tile g = 2 pr + g needs key tiles 0 .. 2 pr + g
+    const int nt_a = 2 * pr + 1, nt_b = 2 * pr + 2;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmQKV);
+        ptx::prefetch_tmap(&tmO);
+    }
+    if (warp == 1 && lane == 0) {
+        ptx::mbar_init(q_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            ptx::mbar_init(k_full(s), 1); ptx::mbar_init(k_empty(s), 1);
+            ptx::mbar_init(v_full(s), 1); ptx::mbar_init(v_empty(s), 1);
+            ptx::mbar_init(s_full(s), 1); ptx::mbar_init(p_full(s), 4); ptx::mbar_init(pv_done(s), 1);
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) {
+        ptx::tmem_alloc(tmem_slot, C::TMEM_COLS);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - base)), 0);
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer (one elected lane per wrapper)
+        ptx::mbar_arrive_expect_tx_w(q_full, 2 * C::TILE);
+#pragma unroll
+        for (int g = 0; g < 2; ++g)
+#pragma unroll
+            for (int c = 0; c < C::NSUB; ++c)
+                ptx::tma_load_3d_w(sQ(g) + c * SUB, &tmQKV, q_full, h * HD + c * 64, (2 * pr + g) * BM, b);
+        for (int j = 0; j < nt_b; ++j) {
+            const int st = j & 1;
+            const uint32_t ph = ((j >> 1) & 1) ^ 1;
+            ptx::mbar_wait(k_empty(st), ph);
+            ptx::mbar_arrive_expect_tx_w(k_full(st), C::TILE);
+#pragma unroll
+            for (int c = 0; c < C::NSUB; ++c)
+                ptx::tma_load_3d_w(sK + st * C::TILE + c * SUB, &tmQKV, k_full(st), d_model + h * HD + c * 64, j * BN, b);
+            ptx::mbar_wait(v_empty(st), ph);
+            ptx::mbar_arrive_expect_tx_w(v_full(st), C::TILE);
+#pragma unroll
+            for (int c = 0; c < C::NSUB; ++c)
+                ptx::tma_load_3d_w(sV + st * C::TILE + c * SUB, &tmQKV, v_full(st), 2 * d_model + h * HD + c * 64, j * BN, b);
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (whole warp converged, see ptx.cuh)
+        constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(128, 128, 0, 0);
+        constexpr uint32_t idesc_pv = ptx::umma_idesc_bf16(128, HD, 0, 1);
+        // S_g(j) = Q_g K_j^T into score buffer g.  The buffer's last reader, PV_g(j-1) (bf16 P aliased onto it), was issued
+        // earlier by this warp: tcgen05.mma executes in issue order, so no barrier is needed for that.
+        auto issue_s = [&](int g, int j) {
+            const int st = j & 1;
+#pragma unroll
+            for (int kk = 0; kk < HD / 16; ++kk) {
+                const uint64_t ad = ptx::umma_desc(sQ(g) + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
+                const uint64_t bd = ptx::umma_desc(sK + st * C::TILE + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
+                ptx::mma_bf16_ss_w(tmem + g * 128, ad, bd, idesc_s, kk > 0 ? 1u : 0u);
+            }
+            ptx::mma_commit_w(s_full(g));
+        };
+        // O_g += P_g(j) V_j : A = bf16 P in TMEM (8 columns per K = 16 slice, aliased onto S_g), B = V_j read MN-major
+        auto issue_pv = [&](int g, int j) {
+            const int st = j & 1;
+            ptx::mbar_wait(p_full(g), j & 1);
+            ptx::mbar_wait(v_full(st), (j >> 1) & 1);
+            ptx::tc_fence_after();
+#pragma unroll
+            for (int kk = 0; kk < BN / 16; ++kk) {
+                const uint64_t bd = ptx::umma_desc(sV + st * C::TILE + kk * 2048, SUB, 1024);
+                ptx::mma_bf16_ts_w(tmem + C::O_COL + g * HD, tmem + g * 128 + 8 * kk, bd, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+            }
+            ptx::mma_commit_w(pv_done(g));
+        };
+        ptx::mbar_wait(q_full, 0);
+        ptx::mbar_wait(k_full(0), 0);
+        ptx::tc_fence_after();
+        issue_s(0, 0);
+        issue_s(1, 0);
+        ptx::mma_commit_w(k_empty(0));
+        for (int j = 0; j < nt_b; ++j) {
+            const bool more_a = j + 1 < nt_a, more_b = j + 1 < nt_b;
+            if (j < nt_a) issue_pv(0, j);
+            if (more_b) {                                    // K_{j+1} is needed by S_A(j+1) and / or S_B(j+1)
+                ptx::mbar_wait(k_full((j + 1) & 1), ((j + 1) >> 1) & 1);
+                ptx::tc_fence_after();
+            }
+            if (more_a) issue_s(0, j + 1);
+            issue_pv(1, j);
+            ptx::mma_commit_w(v_empty(j & 1));               // both PVs of key tile j are issued
+            if (more_b) {
+                issue_s(1, j + 1);
+                ptx::mma_commit_w(k_empty((j + 1) & 1));     // both score MMAs of key tile j+1 are issued
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ softmax + epilogue: group g = query tile 2 pr + g
+        const int g = (warp - 2) >> 2;
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int qt = 2 * pr + g;                           // this group's query tile = its diagonal key tile
+        const int q0 = qt * BM;
+        const int qrow = q0 + row;
+        const int ntiles = qt + 1;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        const uint32_t ts = tmem + lane_off + g * 128;       // this group's score buffer
+        const uint32_t to = tmem + lane_off + C::O_COL + g * HD;
+        float m_used = -INFINITY, l = 0.f;
+        for (int j = 0; j < ntiles; ++j) {
+            ptx::mbar_wait(s_full(g), j & 1);
+            ptx::tc_fence_after();
+            const bool diag = (j == qt);
+            const int k0 = j * BN;
+            // ---- the whole score row (128 fp32) is read from TMEM ONCE and kept in registers
+            uint32_t r[4][32];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32(ts + c * 32, r[c]);
+            ptx::tmem_ld_wait();
+            float mx = -INFINITY;
+            if (diag) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (k0 + c * 32 + i > qrow) r[c][i] = 0xff800000u;      // -inf: exp2 gives exactly 0
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+            const float xmax = mx * scale_log2;
+            const bool need = xmax > m_used + 8.f;          // also true on the first tile (m_used = -inf)
+            const float m_new = need ? xmax : m_used;
+            const float alpha = need ? exp2f(m_used - m_new) : 1.f;
+            // O may be rescaled right away: S_g(j) was issued behind PV_g(j-1), so s_full says PV_g(j-1) has completed, and
+            // PV_g(j) is not issued before this group's p_full arrive below.
+            if (j > 0 && __any_sync(0xffffffffu, need)) {
+#pragma unroll 1
+                for (int c = 0; c < HD / 32; ++c) {
+                    uint32_t o[32];
+                    ptx::tmem_ld_32x32(to + c * 32, o);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                    ptx::tmem_st_32x32(to + c * 32, o);
+                }
+            }
+            l *= alpha;
+            m_used = m_new;
+            // ---- probabilities -> bf16 pairs -> back into the first 64 columns of the score buffer (A operand of PV)
+            float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    const float p0 = exp2f(__uint_as_float(r[c][i]) * scale_log2 - m_used);
+                    const float p1 = exp2f(__uint_as_float(r[c][i + 1]) * scale_log2 - m_used);
+                    rs0 += p0;
+                    rs1 += p1;
+                    pk[i >> 1] = pack_bf16x2(p0, p1);
+                }
+                ptx::tmem_st_32x16(ts + c * 16, pk);
+            }
+            l += rs0 + rs1;
+            ptx::tmem_st_wait();
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(p_full(g));
+        }
+        // ---- epilogue: O / l -> bf16 -> smem (this tile's Q is no longer needed) -> TMA store; LSE -> global
+        ptx::mbar_wait(pv_done(g), (ntiles - 1) & 1);
+        ptx::tc_fence_after();
+        const float inv = l > 0.f ? 1.f / l : 0.f;
+#pragma unroll 1
+        for (int c = 0; c < HD / 32; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld_32x32(to + c * 32, o);
+            ptx::tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2)
+                pk[i >> 1] = pack_bf16x2(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
+            const uint32_t dst = sQ(g) + (c >> 1) * SUB + row * 128;
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+                const uint32_t chunk = (uint32_t)((c & 1) * 4 + ch);
+                const uint32_t addr = dst + ((chunk ^ ((uint32_t)row & 7u)) << 4);
+                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]),
+                             "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3]) : "memory");
+            }
+        }
+        if (qrow < T) lse_out[((size_t)b * H + h) * T + qrow] = (m_used + log2f(l)) * 0.6931471805599453f;
+        ptx::tc_fence_before();
+        ptx::fence_proxy_async_smem();
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+        if (threadIdx.x == 64 + 128 * g && q0 < T) {
+#pragma unroll
+            for (int c = 0; c < C::NSUB; ++c) ptx::tma_store_3d(&tmO, sQ(g) + c * SUB, h * HD + c * 64, q0, b);
+            ptx::tma_store_commit();
+            ptx::tma_store_wait_all<0>();
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem, C::TMEM_COLS);
+    }
+}
+
+template <int HD>
+int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, float scale, cudaStream_t st) {
+    using C = A2Cfg<HD>;
+    const int d = H * HD;
+    CUtensorMap tq, to;
+    if (tma::make_3d(&tq, qkv, 3 * d, T, B, (uint64_t)3 * d * 2, (uint64_t)T * 3 * d * 2, 64, 128, 2)) return -1;
+    if (tma::make_3d(&to, out, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 128, 2)) return -1;
+    auto kern = attn_fwd2_tc_kernel<HD>;
+    static bool cfg = false;
+    if (!cfg) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+        cfg = true;
+    }
+    const int nqt = (T + BM - 1) / BM, npairs = (nqt + 1) / 2;
+    B200_CHECK_CUDA(b200_launch(kern, dim3(npairs * H * B), dim3(NTHREADS_FWD2), C::SMEM, st, tq, to, lse, T, H, H * B, npairs,
+                                scale * 1.4426950408889634f));
+    return 0;
+}
+
 
 
 // =============================================================================================
@@ -778,7 +1063,19 @@ extern "C" int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, i
                                 cudaStream_t st) {
     B200_REQUIRE(hs == 64 || hs == 128, "attn_fwd_tc: head size must be 64 or 128 (got %d)", hs);
     B200_REQUIRE((H * hs) % 8 == 0, "attn_fwd_tc: model width must be a multiple of 8");
-    int rc = hs == 64 ? launch_fwd<64>(qkv, out, lse, B, T, H, scale, st) : launch_fwd<128>(qkv, out, lse, B, T, H, scale, st);
+    // Query tiles per CTA.  hs = 128: two (one CTA per SM, the two softmax groups run half a tile apart: 0.197 -> 0.159 ms on
+    // the 1.3B shape).  hs = 64: one, two CTAs per SM (0.060 ms vs 0.070 ms with two tiles per CTA at T = 1024: only four
+    // tile pairs per (b, h), so the per-CTA prologue / epilogue is no longer hidden behind a co-resident CTA).
+    // B200_ATTN_FWD_TILES=1|2 forces either kernel.
+    static int tiles = -1;
+    if (tiles < 0) {
+        const char* e = getenv("B200_ATTN_FWD_TILES");
+        tiles = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
+    }
+    const int use = tiles ? tiles : (hs == 128 ? 2 : 1);
+    int rc;
+    if (use == 1) rc = hs == 64 ? launch_fwd_1tile<64>(qkv, out, lse, B, T, H, scale, st) : launch_fwd_1tile<128>(qkv, out, lse, B, T, H, scale, st);
+    else rc = hs == 64 ? launch_fwd<64>(qkv, out, lse, B, T, H, scale, st) : launch_fwd<128>(qkv, out, lse, B, T, H, scale, st);
     if (rc) return rc;
     B200_RETURN_LAUNCH_STATUS("attn_fwd_tc");
 }
