@@ -334,7 +334,8 @@ int launch_fwd_1tile(const void* qkv, void* out, float* lse, int B, int T, int H
 // alternates  PV_A(j), S_A(j+1), PV_B(j), S_B(j+1),  so group B runs about half a tile behind group A: while A reads
 // its 64 KB of scores out of TMEM (16 B/clk per lane quarter: 1024 clk) B is in its MUFU.EX2 phase (another 1024 clk),
 // and vice versa - the two phases that bound a tile (profiles/attn_bwd_timeline.md) overlap instead of adding up.
-// Two independent CTAs per SM (the previous hs = 64 layout) start in phase and stay there.
+// The CTAs are persistent (static heaviest-first work list): TMEM, the K/V ring and the barriers stay live across items
+// and each thread stores its own output row, so nothing of an item's prologue or epilogue holds up the next one.
 // ---------------------------------------------------------------------------------------------
 template <int HD> struct A2Cfg {
     static constexpr int NSUB = HD / 64;
@@ -351,7 +352,7 @@ constexpr int NTHREADS_FWD2 = 320;     // TMA warp, MMA warp, 4 softmax warps pe
 
 template <int HD>
 __global__ void __launch_bounds__(NTHREADS_FWD2, 1)
-attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmO,
+attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ out,
                     float* __restrict__ lse_out, int T, int H, int HB, int npairs, float scale_log2) {
     using C = A2Cfg<HD>;
     extern __shared__ uint8_t smem_raw[];
@@ -368,28 +369,34 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
     auto s_full = [&](int g) { return bars + 8u * (9 + g); };      // per query tile, phase = key tile j
     auto p_full = [&](int g) { return bars + 8u * (11 + g); };
     auto pv_done = [&](int g) { return bars + 8u * (13 + g); };
-    const uint32_t tmem_slot = bars + 8u * 15;
+    auto o_free = [&](int g) { return bars + 8u * (15 + g); };    // epilogue of the previous item has read O_g
+    const uint32_t q_empty = bars + 8u * 17;                      // this item's last score MMAs have read Q
+    const uint32_t tmem_slot = bars + 8u * 18;
     uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
-    // 1-D grid in longest-processing-time order: ALL (b, h) of the heaviest (last) pair of query tiles first
-    const int rank = (int)blockIdx.x / HB, hb = (int)blockIdx.x - rank * HB;
-    const int pr = npairs - 1 - rank;
-    const int h = hb % H, b = hb / H;
+    // PERSISTENT: work item i (0 = heaviest) = pair of query tiles npairs-1 - i / HB of (b, h) = i % HB; CTA c takes items
+    // c, c + grid, ...  The K/V ring, the score / P / PV barriers and TMEM stay live across items, so an item's loads and
+    // first score MMAs run under the previous item's last tiles and epilogue.
     const int d_model = H * HD;
-    // tile g = 2 pr + g needs key tiles 0 .. 2 pr + g
-    const int nt_a = 2 * pr + 1, nt_b = 2 * pr + 2;
+    const int nitems = npairs * HB;
+    struct Item { int h, b, pr; };
+    auto decode = [&](int it) {
+        Item w;
+        const int rank = it / HB, hb = it - rank * HB;
+        w.pr = npairs - 1 - rank; w.h = hb % H; w.b = hb / H;
+        return w;
+    };
 
-    if (warp == 0 && lane == 0) {
-        ptx::prefetch_tmap(&tmQKV);
-        ptx::prefetch_tmap(&tmO);
-    }
+    if (warp == 0 && lane == 0) ptx::prefetch_tmap(&tmQKV);
     if (warp == 1 && lane == 0) {
         ptx::mbar_init(q_full, 1);
+        ptx::mbar_init(q_empty, 1);
         for (int s = 0; s < 2; ++s) {
             ptx::mbar_init(k_full(s), 1); ptx::mbar_init(k_empty(s), 1);
             ptx::mbar_init(v_full(s), 1); ptx::mbar_init(v_empty(s), 1);
             ptx::mbar_init(s_full(s), 1); ptx::mbar_init(p_full(s), 4); ptx::mbar_init(pv_done(s), 1);
+            ptx::mbar_init(o_free(s), 4);
         }
         ptx::fence_mbar_init();
     }
@@ -405,34 +412,43 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer (one elected lane per wrapper)
-        ptx::mbar_arrive_expect_tx_w(q_full, 2 * C::TILE);
+        int gk = 0, it_k = 0;                                  // key tiles / items issued so far
+        for (int it = blockIdx.x; it < nitems; it += gridDim.x, ++it_k) {
+            const Item w = decode(it);
+            const int nt_b = 2 * w.pr + 2;
+            ptx::mbar_wait(q_empty, (it_k & 1) ^ 1);
+            ptx::mbar_arrive_expect_tx_w(q_full, 2 * C::TILE);
 #pragma unroll
-        for (int g = 0; g < 2; ++g)
+            for (int g = 0; g < 2; ++g)
 #pragma unroll
-            for (int c = 0; c < C::NSUB; ++c)
-                ptx::tma_load_3d_w(sQ(g) + c * SUB, &tmQKV, q_full, h * HD + c * 64, (2 * pr + g) * BM, b);
-        for (int j = 0; j < nt_b; ++j) {
-            const int st = j & 1;
-            const uint32_t ph = ((j >> 1) & 1) ^ 1;
-            ptx::mbar_wait(k_empty(st), ph);
-            ptx::mbar_arrive_expect_tx_w(k_full(st), C::TILE);
+                for (int c = 0; c < C::NSUB; ++c)
+                    ptx::tma_load_3d_w(sQ(g) + c * SUB, &tmQKV, q_full, w.h * HD + c * 64, (2 * w.pr + g) * BM, w.b);
+            for (int j = 0; j < nt_b; ++j, ++gk) {
+                const int st = gk & 1;
+                const uint32_t ph = ((gk >> 1) & 1) ^ 1;
+                ptx::mbar_wait(k_empty(st), ph);
+                ptx::mbar_arrive_expect_tx_w(k_full(st), C::TILE);
 #pragma unroll
-            for (int c = 0; c < C::NSUB; ++c)
-                ptx::tma_load_3d_w(sK + st * C::TILE + c * SUB, &tmQKV, k_full(st), d_model + h * HD + c * 64, j * BN, b);
-            ptx::mbar_wait(v_empty(st), ph);
-            ptx::mbar_arrive_expect_tx_w(v_full(st), C::TILE);
+                for (int c = 0; c < C::NSUB; ++c)
+                    ptx::tma_load_3d_w(sK + st * C::TILE + c * SUB, &tmQKV, k_full(st), d_model + w.h * HD + c * 64, j * BN, w.b);
+                ptx::mbar_wait(v_empty(st), ph);
+                ptx::mbar_arrive_expect_tx_w(v_full(st), C::TILE);
 #pragma unroll
-            for (int c = 0; c < C::NSUB; ++c)
-                ptx::tma_load_3d_w(sV + st * C::TILE + c * SUB, &tmQKV, v_full(st), 2 * d_model + h * HD + c * 64, j * BN, b);
+                for (int c = 0; c < C::NSUB; ++c)
+                    ptx::tma_load_3d_w(sV + st * C::TILE + c * SUB, &tmQKV, v_full(st), 2 * d_model + w.h * HD + c * 64, j * BN, w.b);
+            }
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (whole warp converged, see ptx.cuh)
         constexpr uint32_t idesc_s = ptx::umma_idesc_bf16(128, 128, 0, 0);
         constexpr uint32_t idesc_pv = ptx::umma_idesc_bf16(128, HD, 0, 1);
-        // S_g(j) = Q_g K_j^T into score buffer g.  The buffer's last reader, PV_g(j-1) (bf16 P aliased onto it), was issued
-        // earlier by this warp: tcgen05.mma executes in issue order, so no barrier is needed for that.
-        auto issue_s = [&](int g, int j) {
-            const int st = j & 1;
+        // S_g(j) = Q_g K_j^T into score buffer g.  The buffer's last reader, the previous PV_g (bf16 P aliased onto it), was
+        // issued earlier by this warp: tcgen05.mma executes in issue order, so no barrier is needed for that.
+        int gk = 0, it_k = 0;                                  // key tiles / items started so far
+        int cnt[2] = {0, 0};                                   // tiles processed so far per query-tile group (barrier phases)
+        // gkj: ring index of the key tile
+        auto issue_s = [&](int g, int gkj) {
+            const int st = gkj & 1;
 #pragma unroll
             for (int kk = 0; kk < HD / 16; ++kk) {
                 const uint64_t ad = ptx::umma_desc(sQ(g) + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
@@ -442,37 +458,44 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             ptx::mma_commit_w(s_full(g));
         };
         // O_g += P_g(j) V_j : A = bf16 P in TMEM (8 columns per K = 16 slice, aliased onto S_g), B = V_j read MN-major
-        auto issue_pv = [&](int g, int j) {
-            const int st = j & 1;
-            ptx::mbar_wait(p_full(g), j & 1);
-            ptx::mbar_wait(v_full(st), (j >> 1) & 1);
+        auto issue_pv = [&](int g, int gkj, bool first) {
+            const int st = gkj & 1;
+            if (first) ptx::mbar_wait(o_free(g), (it_k & 1) ^ 1);     // the previous item's epilogue has read O_g
+            ptx::mbar_wait(p_full(g), cnt[g] & 1);
+            ptx::mbar_wait(v_full(st), (gkj >> 1) & 1);
             ptx::tc_fence_after();
 #pragma unroll
             for (int kk = 0; kk < BN / 16; ++kk) {
                 const uint64_t bd = ptx::umma_desc(sV + st * C::TILE + kk * 2048, SUB, 1024);
-                ptx::mma_bf16_ts_w(tmem + C::O_COL + g * HD, tmem + g * 128 + 8 * kk, bd, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                ptx::mma_bf16_ts_w(tmem + C::O_COL + g * HD, tmem + g * 128 + 8 * kk, bd, idesc_pv, (!first || kk > 0) ? 1u : 0u);
             }
             ptx::mma_commit_w(pv_done(g));
+            ++cnt[g];
         };
-        ptx::mbar_wait(q_full, 0);
-        ptx::mbar_wait(k_full(0), 0);
-        ptx::tc_fence_after();
-        issue_s(0, 0);
-        issue_s(1, 0);
-        ptx::mma_commit_w(k_empty(0));
-        for (int j = 0; j < nt_b; ++j) {
-            const bool more_a = j + 1 < nt_a, more_b = j + 1 < nt_b;
-            if (j < nt_a) issue_pv(0, j);
-            if (more_b) {                                    // K_{j+1} is needed by S_A(j+1) and / or S_B(j+1)
-                ptx::mbar_wait(k_full((j + 1) & 1), ((j + 1) >> 1) & 1);
-                ptx::tc_fence_after();
-            }
-            if (more_a) issue_s(0, j + 1);
-            issue_pv(1, j);
-            ptx::mma_commit_w(v_empty(j & 1));               // both PVs of key tile j are issued
-            if (more_b) {
-                issue_s(1, j + 1);
-                ptx::mma_commit_w(k_empty((j + 1) & 1));     // both score MMAs of key tile j+1 are issued
+        for (int it = blockIdx.x; it < nitems; it += gridDim.x, ++it_k) {
+            const Item w = decode(it);
+            const int nt_a = 2 * w.pr + 1, nt_b = 2 * w.pr + 2;   // tile g = 2 pr + g needs key tiles 0 .. 2 pr + g
+            ptx::mbar_wait(q_full, it_k & 1);
+            ptx::mbar_wait(k_full(gk & 1), (gk >> 1) & 1);
+            ptx::tc_fence_after();
+            issue_s(0, gk);
+            issue_s(1, gk);
+            ptx::mma_commit_w(k_empty(gk & 1));
+            for (int j = 0; j < nt_b; ++j, ++gk) {
+                const bool more_a = j + 1 < nt_a, more_b = j + 1 < nt_b;
+                if (j < nt_a) issue_pv(0, gk, j == 0);
+                if (more_b) {                                    // K_{j+1} is needed by S_A(j+1) and / or S_B(j+1)
+                    ptx::mbar_wait(k_full((gk + 1) & 1), ((gk + 1) >> 1) & 1);
+                    ptx::tc_fence_after();
+                }
+                if (more_a) issue_s(0, gk + 1);
+                issue_pv(1, gk, j == 0);
+                ptx::mma_commit_w(v_empty(gk & 1));              // both PVs of key tile j are issued
+                if (more_b) {
+                    issue_s(1, gk + 1);
+                    ptx::mma_commit_w(k_empty((gk + 1) & 1));    // both score MMAs of key tile j+1 are issued
+                    if (j + 2 == nt_b) ptx::mma_commit_w(q_empty);   // ... and they were the item's last readers of Q
+                }
             }
         }
     } else {
@@ -480,16 +503,20 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
         const int g = (warp - 2) >> 2;
         const int q = warp & 3;
         const int row = q * 32 + lane;
-        const int qt = 2 * pr + g;                           // this group's query tile = its diagonal key tile
-        const int q0 = qt * BM;
-        const int qrow = q0 + row;
-        const int ntiles = qt + 1;
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
         const uint32_t ts = tmem + lane_off + g * 128;       // this group's score buffer
         const uint32_t to = tmem + lane_off + C::O_COL + g * HD;
+        int cnt = 0;                                         // tiles processed so far by this group (barrier phases)
+        for (int it = blockIdx.x; it < nitems; it += gridDim.x) {
+        const Item w = decode(it);
+        const int h = w.h, b = w.b;
+        const int qt = 2 * w.pr + g;                         // this group's query tile = its diagonal key tile
+        const int q0 = qt * BM;
+        const int qrow = q0 + row;
+        const int ntiles = qt + 1;
         float m_used = -INFINITY, l = 0.f;
-        for (int j = 0; j < ntiles; ++j) {
-            ptx::mbar_wait(s_full(g), j & 1);
+        for (int j = 0; j < ntiles; ++j, ++cnt) {
+            ptx::mbar_wait(s_full(g), cnt & 1);
             ptx::tc_fence_after();
             const bool diag = (j == qt);
             const int k0 = j * BN;
@@ -550,38 +577,32 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_cons
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(p_full(g));
         }
-        // ---- epilogue: O / l -> bf16 -> smem (this tile's Q is no longer needed) -> TMA store; LSE -> global
-        ptx::mbar_wait(pv_done(g), (ntiles - 1) & 1);
+        // ---- epilogue: O / l -> bf16 -> global (each thread writes its own row); LSE -> global
+        ptx::mbar_wait(pv_done(g), (cnt - 1) & 1);
         ptx::tc_fence_after();
         const float inv = l > 0.f ? 1.f / l : 0.f;
+        bf16* orow = out + ((size_t)b * T + qrow) * d_model + h * HD;
 #pragma unroll 1
         for (int c = 0; c < HD / 32; ++c) {
             uint32_t o[32];
             ptx::tmem_ld_32x32(to + c * 32, o);
             ptx::tmem_ld_wait();
-            uint32_t pk[16];
+            if (qrow < T) {
 #pragma unroll
-            for (int i = 0; i < 32; i += 2)
-                pk[i >> 1] = pack_bf16x2(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv);
-            const uint32_t dst = sQ(g) + (c >> 1) * SUB + row * 128;
-#pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-                const uint32_t chunk = (uint32_t)((c & 1) * 4 + ch);
-                const uint32_t addr = dst + ((chunk ^ ((uint32_t)row & 7u)) << 4);
-                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]),
-                             "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3]) : "memory");
+                for (int i = 0; i < 32; i += 8)
+                    *reinterpret_cast<uint4*>(orow + c * 32 + i) =
+                        make_uint4(pack_bf16x2(__uint_as_float(o[i]) * inv, __uint_as_float(o[i + 1]) * inv),
+                                   pack_bf16x2(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv),
+                                   pack_bf16x2(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv),
+                                   pack_bf16x2(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv));
             }
         }
         if (qrow < T) lse_out[((size_t)b * H + h) * T + qrow] = (m_used + log2f(l)) * 0.6931471805599453f;
+        // O_g may be overwritten by the next item's first PV
         ptx::tc_fence_before();
-        ptx::fence_proxy_async_smem();
-        asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
-        if (threadIdx.x == 64 + 128 * g && q0 < T) {
-#pragma unroll
-            for (int c = 0; c < C::NSUB; ++c) ptx::tma_store_3d(&tmO, sQ(g) + c * SUB, h * HD + c * 64, q0, b);
-            ptx::tma_store_commit();
-            ptx::tma_store_wait_all<0>();
-        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(o_free(g));
+        }   // items
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -595,9 +616,8 @@ template <int HD>
 int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, float scale, cudaStream_t st) {
     using C = A2Cfg<HD>;
     const int d = H * HD;
-    CUtensorMap tq, to;
+    CUtensorMap tq;
     if (tma::make_3d(&tq, qkv, 3 * d, T, B, (uint64_t)3 * d * 2, (uint64_t)T * 3 * d * 2, 64, 128, 2)) return -1;
-    if (tma::make_3d(&to, out, d, T, B, (uint64_t)d * 2, (uint64_t)T * d * 2, 64, 128, 2)) return -1;
     auto kern = attn_fwd2_tc_kernel<HD>;
     static bool cfg = false;
     if (!cfg) {
@@ -605,7 +625,9 @@ int launch_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, floa
         cfg = true;
     }
     const int nqt = (T + BM - 1) / BM, npairs = (nqt + 1) / 2;
-    B200_CHECK_CUDA(b200_launch(kern, dim3(npairs * H * B), dim3(NTHREADS_FWD2), C::SMEM, st, tq, to, lse, T, H, H * B, npairs,
+    const int nitems = npairs * H * B;
+    const int grid = nitems < b200_num_sms() ? nitems : b200_num_sms();
+    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NTHREADS_FWD2), C::SMEM, st, tq, (bf16*)out, lse, T, H, H * B, npairs,
                                 scale * 1.4426950408889634f));
     return 0;
 }

@@ -24,7 +24,12 @@ def graph_time(fn, reps=5):
     return min(ts) / L
 
 
-shapes = ((64, 12, 16, 1024), (128, 16, 8, 2048)) if len(sys.argv) < 2 else ((int(sys.argv[1]),) + ((12, 16, 1024) if sys.argv[1] == "64" else (16, 8, 2048)),)
+# usage: bench_attn.py            -> the two model shapes
+#        bench_attn.py hs H B T    -> one custom shape
+if len(sys.argv) == 5:
+    shapes = (tuple(int(v) for v in sys.argv[1:5]),)
+else:
+    shapes = ((64, 12, 16, 1024), (128, 16, 8, 2048))
 for hs, H, B, T in shapes:
     qkvs = [torch.randn(B * T, 3 * H * hs, device="cuda").to(BF16) for _ in range(L)]
     outs, lses = zip(*[ops.attn_fwd(q, B, T, H, hs) for q in qkvs])
