@@ -1081,25 +1081,30 @@ int launch_bwd(const void* qkv, const void* out, const void* dout, const float* 
 
 }  // namespace
 
-extern "C" int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale,
-                                cudaStream_t st) {
+extern "C" int b200_attn_fwd_tc_tiles(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale,
+                                      int tiles, cudaStream_t st) {
     B200_REQUIRE(hs == 64 || hs == 128, "attn_fwd_tc: head size must be 64 or 128 (got %d)", hs);
     B200_REQUIRE((H * hs) % 8 == 0, "attn_fwd_tc: model width must be a multiple of 8");
-    // Query tiles per CTA.  hs = 128: two (one CTA per SM, the two softmax groups run half a tile apart: 0.197 -> 0.159 ms on
-    // the 1.3B shape).  hs = 64: one, two CTAs per SM (0.060 ms vs 0.070 ms with two tiles per CTA at T = 1024: only four
-    // tile pairs per (b, h), so the per-CTA prologue / epilogue is no longer hidden behind a co-resident CTA).
-    // B200_ATTN_FWD_TILES=1|2 forces either kernel.
-    static int tiles = -1;
-    if (tiles < 0) {
+    B200_REQUIRE(tiles >= 0 && tiles <= 2, "attn_fwd_tc: tiles per CTA must be 0 (default), 1 or 2");
+    // Query tiles per CTA.  hs = 128: two (one persistent CTA per SM, the two softmax groups run half a tile apart:
+    // 0.197 -> 0.159 ms on the 1.3B shape).  hs = 64: one, two CTAs per SM (0.060 ms; the two-tile kernel measures
+    // 0.061 ms there).  B200_ATTN_FWD_TILES=1|2 overrides the default.
+    static int env_tiles = -1;
+    if (env_tiles < 0) {
         const char* e = getenv("B200_ATTN_FWD_TILES");
-        tiles = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
+        env_tiles = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
     }
-    const int use = tiles ? tiles : (hs == 128 ? 2 : 1);
+    const int use = tiles ? tiles : (env_tiles ? env_tiles : (hs == 128 ? 2 : 1));
     int rc;
     if (use == 1) rc = hs == 64 ? launch_fwd_1tile<64>(qkv, out, lse, B, T, H, scale, st) : launch_fwd_1tile<128>(qkv, out, lse, B, T, H, scale, st);
     else rc = hs == 64 ? launch_fwd<64>(qkv, out, lse, B, T, H, scale, st) : launch_fwd<128>(qkv, out, lse, B, T, H, scale, st);
     if (rc) return rc;
     B200_RETURN_LAUNCH_STATUS("attn_fwd_tc");
+}
+
+extern "C" int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale,
+                                cudaStream_t st) {
+    return b200_attn_fwd_tc_tiles(qkv, out, lse, B, T, H, hs, scale, 0, st);
 }
 
 // delta: [B, H, T] fp32 scratch (row sums of dO * O); nothing else is needed.

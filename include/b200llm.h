@@ -112,6 +112,9 @@ int b200_ce_grad(void* logits, long long ld, const float* lse, const long long* 
 int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale, cudaStream_t st);
 /* same contract on tcgen05/TMEM/TMA (S and O accumulate in tensor memory; the default forward) */
 int b200_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale, cudaStream_t st);
+/* Same, with the number of query tiles per CTA chosen by the caller: 1 (two CTAs per SM at hs = 64) or 2 (persistent
+ * CTAs, two softmax groups half a tile apart); 0 = the default of b200_attn_fwd_tc (1 for hs = 64, 2 for hs = 128). */
+int b200_attn_fwd_tc_tiles(const void* qkv, void* out, float* lse, int B, int T, int H, int hs, float scale, int tiles, cudaStream_t st);
 /* dqkv [B*T, 3*H*hs] bf16; delta [B, H, T] fp32 scratch; dq_acc [B*T, H*hs] fp32 scratch */
 int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t st);
 

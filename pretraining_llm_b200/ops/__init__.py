@@ -215,7 +215,12 @@ def attn_fwd(qkv, B, T, H, hs, out=None, lse=None, impl: Optional[str] = None):
     if lse is None:
         lse = torch.empty(B, H, T, device=qkv.device, dtype=F32)
     L = lib.load()
-    fn = L.b200_attn_fwd_tc if (impl or ATTN_FWD_IMPL) == "tc" else L.b200_attn_fwd
+    which = impl or ATTN_FWD_IMPL
+    if which in ("tc1", "tc2"):      # tcgen05 kernel with 1 / 2 query tiles per CTA forced (tests, benchmarks)
+        _chk(L.b200_attn_fwd_tc_tiles(_p(qkv), _p(out), _p(lse), B, T, H, hs, 1.0 / math.sqrt(hs), int(which[2]), _st()),
+             "attn_fwd")
+        return out, lse
+    fn = L.b200_attn_fwd_tc if which == "tc" else L.b200_attn_fwd
     _chk(fn(_p(qkv), _p(out), _p(lse), B, T, H, hs, 1.0 / math.sqrt(hs), _st()), "attn_fwd")
     return out, lse
 

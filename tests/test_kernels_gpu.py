@@ -290,6 +290,23 @@ def test_flash_attention_fwd_bwd(ops, hs, T, impl):
         assert err < 2e-2, (name, err.item())
 
 
+@pytest.mark.parametrize("tiles", ["tc1", "tc2"])
+@pytest.mark.parametrize("hs", [64, 128])
+@pytest.mark.parametrize("T", [100, 384, 640, 1024])
+def test_flash_attention_fwd_both_layouts(ops, hs, T, tiles):
+    """One and two query tiles per CTA (the default picks by head size): same output and log-sum-exp.  T = 100 / 384 / 640
+    give an odd number of 128-row tiles, i.e. a last pair whose second tile is empty or partial; B*H*pairs > #SMs at
+    T = 1024 makes the persistent CTAs walk several work items."""
+    torch.manual_seed(21)
+    B, H = (25, 6) if T == 1024 else (2, 3)
+    qkv = _rand(B * T, 3 * H * hs)
+    out, lse = ops.attn_fwd(qkv, B, T, H, hs, impl=tiles)
+    ref = _ref_attn(qkv.float(), B, T, H, hs)
+    assert _rel(out, ref) < 8e-3, _rel(out, ref)
+    out2, lse2 = ops.attn_fwd(qkv, B, T, H, hs, impl="mma")
+    assert torch.allclose(lse, lse2, atol=2e-3, rtol=1e-3)
+
+
 @pytest.mark.parametrize("hs", [64, 128])
 def test_decode_attention(ops, hs):
     torch.manual_seed(9)
