@@ -292,13 +292,13 @@ def test_flash_attention_fwd_bwd(ops, hs, T, impl):
 
 @pytest.mark.parametrize("tiles", ["tc1", "tc2"])
 @pytest.mark.parametrize("hs", [64, 128])
-@pytest.mark.parametrize("T", [100, 384, 640, 1024])
+@pytest.mark.parametrize("T", [100, 384, 640, 1024, 2048])
 def test_flash_attention_fwd_both_layouts(ops, hs, T, tiles):
     """One and two query tiles per CTA (the default picks by head size): same output and log-sum-exp.  T = 100 / 384 / 640
     give an odd number of 128-row tiles, i.e. a last pair whose second tile is empty or partial; B*H*pairs > #SMs at
     T = 1024 makes the persistent CTAs walk several work items."""
     torch.manual_seed(21)
-    B, H = (25, 6) if T == 1024 else (2, 3)
+    B, H = (25, 6) if T == 1024 else ((3, 4) if T == 2048 else (2, 3))
     qkv = _rand(B * T, 3 * H * hs)
     out, lse = ops.attn_fwd(qkv, B, T, H, hs, impl=tiles)
     ref = _ref_attn(qkv.float(), B, T, H, hs)
