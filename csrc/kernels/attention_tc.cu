@@ -36,7 +36,7 @@ constexpr int NTHREADS_BWD = 64 + 32 * BWD_EW_WARPS;   // TMA warp + MMA warp + 
 
 // Optional forward timeline (tools/attn_trace.cu, -DATTN_TRACE): CTA 0, clock64() at the hand-offs.  Compiled out otherwise.
 #ifdef ATTN_TRACE
-__device__ long long g_attn_trace_fwd[2][64][8];   // [role: 0 MMA warp, 1 softmax warp 2][tile][event]
+__device__ long long g_attn_trace_fwd[3][64][8];   // [role: 0 MMA warp, 1 / 2 softmax group A / B (one warp)][tile][event]
 #define TRACEF(role, n, k) do { if (blockIdx.x == 0 && (n) < 64) g_attn_trace_fwd[role][n][k] = clock64(); } while (0)
 #else
 #define TRACEF(role, n, k) do { } while (0)
@@ -341,11 +341,17 @@ template <int HD> struct A2Cfg {
     static constexpr int NSUB = HD / 64;
     static constexpr int TILE = NSUB * SUB;
     static constexpr int KV = 2;                           // K / V ring depth
-    static constexpr int TMEM_COLS = 512;                  // S_A 0 | S_B 128 | O_A 256 | O_B 256 + HD
-    static constexpr int O_COL = 256;
+    // TMEM columns.  hs = 128: S_A 0 | S_B 128 | O_A 256 | O_B 384, the bf16 P of a tile written over its scores.
+    // hs = 64 has room to keep P apart (PSEP): S_A 0 | S_B 128 | P_A 256 | P_B 320 | O_A 384 | O_B 448.  Then S_g(j+1) can be
+    // issued as soon as the softmax group has READ S_g(j), i.e. it runs under the group's exponentials, and the group
+    // never waits for scores: per tile and group the chain was softmax -> PV -> S -> softmax.
+    static constexpr bool PSEP = HD == 64;
+    static constexpr int TMEM_COLS = 512;
+    static constexpr int P_COL = PSEP ? 256 : 0, P_STRIDE = PSEP ? 64 : 128;
+    static constexpr int O_COL = PSEP ? 384 : 256;
     static constexpr int USED = 2 * TILE + 2 * KV * TILE + 256;   // Q_A Q_B | K ring | V ring | barriers
     static constexpr int SMEM = USED + 1024;
-    static_assert(O_COL + 2 * HD <= 512, "TMEM budget");
+    static_assert(O_COL + 2 * HD <= 512 && (!PSEP || P_COL + 2 * P_STRIDE <= O_COL), "TMEM budget");
     static_assert(SMEM <= 232448, "smem budget");
 };
 constexpr int NTHREADS_FWD2 = 320;     // TMA warp, MMA warp, 4 softmax warps per query tile
@@ -371,7 +377,8 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
     auto pv_done = [&](int g) { return bars + 8u * (13 + g); };
     auto o_free = [&](int g) { return bars + 8u * (15 + g); };    // epilogue of the previous item has read O_g
     const uint32_t q_empty = bars + 8u * 17;                      // this item's last score MMAs have read Q
-    const uint32_t tmem_slot = bars + 8u * 18;
+    auto s_read = [&](int g) { return bars + 8u * (18 + g); };    // PSEP: the softmax group holds S_g in registers
+    const uint32_t tmem_slot = bars + 8u * 20;
     uint8_t* gen = smem_raw + (base - ptx::smem_u32(smem_raw));
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
@@ -396,7 +403,7 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
             ptx::mbar_init(k_full(s), 1); ptx::mbar_init(k_empty(s), 1);
             ptx::mbar_init(v_full(s), 1); ptx::mbar_init(v_empty(s), 1);
             ptx::mbar_init(s_full(s), 1); ptx::mbar_init(p_full(s), 4); ptx::mbar_init(pv_done(s), 1);
-            ptx::mbar_init(o_free(s), 4);
+            ptx::mbar_init(o_free(s), 4); ptx::mbar_init(s_read(s), 4);
         }
         ptx::fence_mbar_init();
     }
@@ -445,10 +452,16 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
         // S_g(j) = Q_g K_j^T into score buffer g.  The buffer's last reader, the previous PV_g (bf16 P aliased onto it), was
         // issued earlier by this warp: tcgen05.mma executes in issue order, so no barrier is needed for that.
         int gk = 0, it_k = 0;                                  // key tiles / items started so far
-        int cnt[2] = {0, 0};                                   // tiles processed so far per query-tile group (barrier phases)
+        int cnt[2] = {0, 0};                                   // PVs issued so far per query-tile group (barrier phases)
+        int scnt[2] = {0, 0};                                  // score tiles issued so far per group
         // gkj: ring index of the key tile
         auto issue_s = [&](int g, int gkj) {
             const int st = gkj & 1;
+            if (C::PSEP && scnt[g] > 0) {                      // the previous scores of this group are in registers
+                ptx::mbar_wait(s_read(g), (scnt[g] - 1) & 1);
+                ptx::tc_fence_after();
+            }
+            ++scnt[g];
 #pragma unroll
             for (int kk = 0; kk < HD / 16; ++kk) {
                 const uint64_t ad = ptx::umma_desc(sQ(g) + (kk >> 2) * SUB + (kk & 3) * 32, 16, 1024);
@@ -456,6 +469,7 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
                 ptx::mma_bf16_ss_w(tmem + g * 128, ad, bd, idesc_s, kk > 0 ? 1u : 0u);
             }
             ptx::mma_commit_w(s_full(g));
+            if (it_k == 0) TRACEF(0, gkj, g == 0 ? 0 : 2);
         };
         // O_g += P_g(j) V_j : A = bf16 P in TMEM (8 columns per K = 16 slice, aliased onto S_g), B = V_j read MN-major
         auto issue_pv = [&](int g, int gkj, bool first) {
@@ -467,9 +481,11 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
 #pragma unroll
             for (int kk = 0; kk < BN / 16; ++kk) {
                 const uint64_t bd = ptx::umma_desc(sV + st * C::TILE + kk * 2048, SUB, 1024);
-                ptx::mma_bf16_ts_w(tmem + C::O_COL + g * HD, tmem + g * 128 + 8 * kk, bd, idesc_pv, (!first || kk > 0) ? 1u : 0u);
+                ptx::mma_bf16_ts_w(tmem + C::O_COL + g * HD, tmem + C::P_COL + g * C::P_STRIDE + 8 * kk, bd, idesc_pv,
+                                   (!first || kk > 0) ? 1u : 0u);
             }
             ptx::mma_commit_w(pv_done(g));
+            if (it_k == 0) TRACEF(0, gkj, g == 0 ? 1 : 3);
             ++cnt[g];
         };
         for (int it = blockIdx.x; it < nitems; it += gridDim.x, ++it_k) {
@@ -483,18 +499,32 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
             ptx::mma_commit_w(k_empty(gk & 1));
             for (int j = 0; j < nt_b; ++j, ++gk) {
                 const bool more_a = j + 1 < nt_a, more_b = j + 1 < nt_b;
-                if (j < nt_a) issue_pv(0, gk, j == 0);
                 if (more_b) {                                    // K_{j+1} is needed by S_A(j+1) and / or S_B(j+1)
                     ptx::mbar_wait(k_full((gk + 1) & 1), ((gk + 1) >> 1) & 1);
                     ptx::tc_fence_after();
                 }
-                if (more_a) issue_s(0, gk + 1);
-                issue_pv(1, gk, j == 0);
-                ptx::mma_commit_w(v_empty(gk & 1));              // both PVs of key tile j are issued
-                if (more_b) {
-                    issue_s(1, gk + 1);
-                    ptx::mma_commit_w(k_empty((gk + 1) & 1));    // both score MMAs of key tile j+1 are issued
-                    if (j + 2 == nt_b) ptx::mma_commit_w(q_empty);   // ... and they were the item's last readers of Q
+                if (C::PSEP) {
+                    // P has its own columns: the next scores go out first (each waits only for its group to have READ the
+                    // current ones), the PVs follow when the probabilities are written
+                    if (more_a) issue_s(0, gk + 1);
+                    if (more_b) {
+                        issue_s(1, gk + 1);
+                        ptx::mma_commit_w(k_empty((gk + 1) & 1));
+                        if (j + 2 == nt_b) ptx::mma_commit_w(q_empty);
+                    }
+                    if (j < nt_a) issue_pv(0, gk, j == 0);
+                    issue_pv(1, gk, j == 0);
+                    ptx::mma_commit_w(v_empty(gk & 1));
+                } else {
+                    if (j < nt_a) issue_pv(0, gk, j == 0);
+                    if (more_a) issue_s(0, gk + 1);
+                    issue_pv(1, gk, j == 0);
+                    ptx::mma_commit_w(v_empty(gk & 1));              // both PVs of key tile j are issued
+                    if (more_b) {
+                        issue_s(1, gk + 1);
+                        ptx::mma_commit_w(k_empty((gk + 1) & 1));    // both score MMAs of key tile j+1 are issued
+                        if (j + 2 == nt_b) ptx::mma_commit_w(q_empty);   // ... and they were the item's last readers of Q
+                    }
                 }
             }
         }
@@ -505,8 +535,10 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
         const int row = q * 32 + lane;
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
         const uint32_t ts = tmem + lane_off + g * 128;       // this group's score buffer
+        const uint32_t tp = tmem + lane_off + C::P_COL + g * C::P_STRIDE;   // ... and where its bf16 P goes
         const uint32_t to = tmem + lane_off + C::O_COL + g * HD;
         int cnt = 0;                                         // tiles processed so far by this group (barrier phases)
+        int ocnt = 0;                                        // ... and by the OTHER group, up to the start of this item
         for (int it = blockIdx.x; it < nitems; it += gridDim.x) {
         const Item w = decode(it);
         const int h = w.h, b = w.b;
@@ -516,8 +548,19 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
         const int ntiles = qt + 1;
         float m_used = -INFINITY, l = 0.f;
         for (int j = 0; j < ntiles; ++j, ++cnt) {
+            const bool tr = (it == (int)blockIdx.x) && lane == 0 && q == 2;
+            if (tr) TRACEF(1 + g, j, 0);
             ptx::mbar_wait(s_full(g), cnt & 1);
             ptx::tc_fence_after();
+            if (tr) TRACEF(1 + g, j, 1);
+            // PSEP only (hs = 64, where nothing else orders the groups): the TMEM-read phase is a token the two groups pass
+            // back and forth (A_0 B_0 A_1 B_1 ...) so that they do not read tensor memory at the same time.  Measured
+            // neutral: the timeline shows the tile is bound by MUFU.EX2 (two groups x 128 exp per thread = 2048 clk per
+            // pair of tiles on each scheduler) once the reads are out of the way.
+            if (C::PSEP && (g == 0 ? (j > 0) : (j < ntiles - 1))) {
+                // A_j waits for B_{j-1}; B_j waits for A_j (B's last tile has no A counterpart)
+                ptx::mbar_wait(s_read(g ^ 1), (ocnt + (g == 0 ? j - 1 : j)) & 1);
+            }
             const bool diag = (j == qt);
             const int k0 = j * BN;
             // ---- the whole score row (128 fp32) is read from TMEM ONCE and kept in registers
@@ -525,6 +568,21 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
 #pragma unroll
             for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32(ts + c * 32, r[c]);
             ptx::tmem_ld_wait();
+            {
+                // scores are in registers: the other group may start its TMEM reads, and (PSEP) the MMA warp may overwrite
+                // the buffer with the next tile's
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(s_read(g));
+            }
+            if (C::PSEP) {
+                // P_g and O_g belong to PV_g of the previous tile until it has completed (with P aliased onto S this is
+                // implied by s_full; here the scores were issued BEFORE that PV)
+                if (j > 0) {
+                    ptx::mbar_wait(pv_done(g), (cnt - 1) & 1);
+                    ptx::tc_fence_after();
+                }
+            }
             float mx = -INFINITY;
             if (diag) {
 #pragma unroll
@@ -537,6 +595,7 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
             for (int c = 0; c < 4; ++c)
 #pragma unroll
                 for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[c][i]));
+            if (tr) TRACEF(1 + g, j, 2);
             const float xmax = mx * scale_log2;
             const bool need = xmax > m_used + 8.f;          // also true on the first tile (m_used = -inf)
             const float m_new = need ? xmax : m_used;
@@ -569,13 +628,15 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
                     rs1 += p1;
                     pk[i >> 1] = pack_bf16x2(p0, p1);
                 }
-                ptx::tmem_st_32x16(ts + c * 16, pk);
+                ptx::tmem_st_32x16(tp + c * 16, pk);
             }
             l += rs0 + rs1;
+            if (tr) TRACEF(1 + g, j, 3);
             ptx::tmem_st_wait();
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(p_full(g));
+            if (tr) TRACEF(1 + g, j, 4);
         }
         // ---- epilogue: O / l -> bf16 -> global (each thread writes its own row); LSE -> global
         ptx::mbar_wait(pv_done(g), (cnt - 1) & 1);
@@ -602,6 +663,7 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(o_free(g));
+        ocnt += 2 * w.pr + (g ^ 1) + 1;
         }   // items
     }
     ptx::tc_fence_before();

@@ -25,16 +25,19 @@ int main(int argc, char** argv) {
         if (b200_attn_bwd_tc(qkv, out, dout, lse, delta, dqkv, B, T, H, hs, scale, 0)) { printf("bwd: %s\n", b200_last_error()); return 1; }
     if (cudaDeviceSynchronize() != cudaSuccess) { printf("sync failed\n"); return 1; }
     {
-        static long long f[2][64][8];
+        static long long f[3][64][8];
         cudaMemcpyFromSymbol(f, g_attn_trace_fwd, sizeof(f));
         const long long t0 = f[0][0][0];
-        printf("pass=FWD hs=%d, CTA 0 (last query tile); clk relative to the MMA warp's first k_full\n", hs);
-        printf("%3s | %49s | %53s\n", "j", "mma: k_full s_issued p_full v_full pv_issued", "softmax: top s_full max_done rescaled exp_done arrived");
+        printf("pass=FWD hs=%d, CTA 0, first work item (last pair of query tiles); clk relative to the first S_A issue\n", hs);
+        printf("%3s | %35s | %44s | %44s\n", "j", "mma: S_A PV_A S_B PV_B issued", "group A: top s_full loaded exp_done arrived",
+               "group B: top s_full loaded exp_done arrived");
         for (int n = 0; n < 16; ++n) {
             printf("%3d |", n);
-            for (int k = 0; k < 5; ++k) printf(" %8lld", f[0][n][k] ? f[0][n][k] - t0 : 0);
+            for (int k = 0; k < 4; ++k) printf(" %8lld", f[0][n][k] ? f[0][n][k] - t0 : 0);
             printf(" |");
-            for (int k = 0; k < 6; ++k) printf(" %8lld", f[1][n][k] ? f[1][n][k] - t0 : 0);
+            for (int k = 0; k < 5; ++k) printf(" %8lld", f[1][n][k] ? f[1][n][k] - t0 : 0);
+            printf(" |");
+            for (int k = 0; k < 5; ++k) printf(" %8lld", f[2][n][k] ? f[2][n][k] - t0 : 0);
             printf("\n");
         }
     }
