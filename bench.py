@@ -32,6 +32,7 @@ MODELS = {
     "1.3b": dict(n_blocks=24, n_embed=2048, n_head=16, context_length=2048, vocab_size=50304),
 }
 LR = 5e-4
+_RESULT_OUT = None
 
 
 def parse():
@@ -175,7 +176,7 @@ def run_ours(args):
         e2e = {"value": tokens / dt, "unit": "tokens/s", "h2d_bytes_per_step": 2 * B * T * 8 * world,
                "d2h_bytes_per_step": 4 * world, "ms_per_step": dt * 1e3 / args.steps}
     if rank == 0:
-        print(json.dumps({
+        emit(json.dumps({
             "metric": "train tokens/sec (device-timed, max over ranks)", "value": value, "unit": "tokens/s",
             "impl": "ours", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -188,7 +189,7 @@ def run_ours(args):
                              "is far larger than the 126 MB L2"},
             "final_loss": final_loss, "clocks": clk, "e2e": e2e, "gpu_launches": per_step * args.steps,
             "gpu_launches_per_step": per_step,
-        }), flush=True)
+        }))
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
@@ -201,14 +202,34 @@ def run_reference(args):
     from baseline.ref_import import reference_root
     root = reference_root()
     if root is None:
-        print(json.dumps({"impl": "reference", "unavailable": "reference tree not found (baseline/_ref)"}))
+        emit(json.dumps({"impl": "reference", "unavailable": "reference tree not found (baseline/_ref)"}))
         return
     from baseline.harness import run_reference_bench
     run_reference_bench(args, root, MODELS[args.model], LR)
 
 
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL announces its version on rank 0), so
+    the real stdout is kept aside for the result line and file descriptor 1 is pointed at stderr for everything else."""
+    global _RESULT_OUT
+    try:
+        sys.stdout.flush()
+        _RESULT_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)                # C-level writers (NCCL's printf) now land on stderr
+        sys.stdout = _RESULT_OUT     # Python-level print() keeps the real stdout (the reference harness prints its line)
+    except OSError:
+        _RESULT_OUT = sys.stdout
+
+
+def emit(line: str) -> None:
+    out = _RESULT_OUT if _RESULT_OUT is not None else sys.stdout
+    out.write(line + "\n")
+    out.flush()
+
+
 def main():
     args = parse()
+    _claim_stdout()
     if args.impl == "reference":
         try:
             run_reference(args)
@@ -216,7 +237,7 @@ def main():
             import traceback
             traceback.print_exc()
             if int(os.environ.get("RANK", 0)) == 0:
-                print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {str(e)[:200]}"}))
+                emit(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {str(e)[:200]}"}))
     else:
         run_ours(args)
 
