@@ -73,6 +73,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     assert out.shape == (M, N) and out.stride(-1) == 1
     out_f32 = out.dtype == F32
     assert out_f32 or out.dtype == BF16
+    if stats is not None:
+        assert bn in (0, 256), "the CE-statistics epilogue is used with 256-column tiles"
+        assert stats.dtype == F32 and stats.is_contiguous() and stats.numel() >= gemm_stats_entries(N) * M * 2, \
+            f"stats needs {gemm_stats_entries(N)} x {M} x 2 floats (see ops.gemm_stats_entries)"
     for t in (relu_bits_out, relu_bits):
         assert t is None or (t.dtype == torch.int64 and t.is_contiguous() and t.shape == (M, (N + 63) // 64))
     L = lib.load()
@@ -94,6 +98,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
             _st())
     _chk(rc, "gemm")
     return out
+
+
+def gemm_stats_entries(N: int, bn: int = 256) -> int:
+    """Rows of the `stats` tensor ([entries, M, 2] fp32) the GEMM epilogue fills: one (max, sum exp) pair per n-tile of width
+    `bn` and per epilogue warp group (two groups for tiles of 128 or 256 columns)."""
+    return (2 if bn >= 128 else 1) * ((N + bn - 1) // bn)
 
 
 def gemm_skinny(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None, *, bias=None, relu: bool = False,

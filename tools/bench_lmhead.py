@@ -7,7 +7,7 @@ BF16 = torch.bfloat16
 M, N, K = 16384, 50304, 768
 x = torch.randn(M, K, device="cuda").to(BF16); w = (torch.randn(N, K, device="cuda") * 0.02).to(BF16)
 bias = torch.zeros(N, device="cuda"); out = torch.empty(M, N, device="cuda", dtype=BF16)
-stats = torch.empty((N + 255) // 256, M, 2, device="cuda")
+stats = torch.empty(ops.gemm_stats_entries(N), M, 2, device="cuda")
 
 
 def t(fn, reps=7):
