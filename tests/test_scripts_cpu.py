@@ -62,3 +62,22 @@ def test_data_download_offline_message():
     r = _run(["scripts/data_download.py"], {})
     assert r.returncode == 0
     assert "could not download" in r.stdout or "documents" in r.stdout
+
+
+def test_bench_prints_exactly_one_json_line_on_stdout():
+    """The driver parses bench.py's stdout: one JSON line, whatever libraries print (they are routed to stderr)."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert d.get("impl") == "reference"          # on a CPU box: {"impl": "reference", "unavailable": ...}
+
+
+def test_gemm_stats_entries_contract():
+    from pretraining_llm_b200 import ops
+    assert ops.gemm_stats_entries(50304) == 2 * 197        # 256-column tiles x 2 epilogue groups
+    assert ops.gemm_stats_entries(256) == 2 and ops.gemm_stats_entries(257) == 4
+    assert ops.gemm_stats_entries(1000, bn=64) == 16       # 64-column tiles: one group
