@@ -600,8 +600,8 @@ attn_fwd2_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict_
             const bool need = xmax > m_used + 8.f;          // also true on the first tile (m_used = -inf)
             const float m_new = need ? xmax : m_used;
             const float alpha = need ? exp2f(m_used - m_new) : 1.f;
-            // O may be rescaled right away: S_g(j) was issued behind PV_g(j-1), so s_full says PV_g(j-1) has completed, and
-            // PV_g(j) is not issued before this group's p_full arrive below.
+            // O may be rescaled right away: PV_g(j-1) has completed (aliased P: S_g(j) was issued behind it, so s_full says so;
+            // PSEP: the pv_done wait above), and PV_g(j) is not issued before this group's p_full arrive below.
             if (j > 0 && __any_sync(0xffffffffu, need)) {
 #pragma unroll 1
                 for (int c = 0; c < HD / 32; ++c) {
