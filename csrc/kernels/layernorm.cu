@@ -293,16 +293,14 @@ extern "C" int b200_ln_bwd_nparts(int M, int d) {
     return max(grid, 1);
 }
 
-extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* rstd,
-                           const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16,
-                           float* partial, float* dgamma, float* dbeta, float* colsum, int M, int d,
-                           int accumulate, cudaStream_t st) {
+// main kernel of the backward: dx (+ residual gradient, + bf16 copy) and one partial row of (dgamma, dbeta[, colsum]) per CTA
+static int ln_bwd_main(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma,
+                       const float* dx_in, float* dx_out, void* dx_bf16, float* partial, bool cs, int M, int d,
+                       int* grid_out, cudaStream_t st) {
     LnCfg cfg;
     B200_REQUIRE(ln_cfg(d, &cfg), "ln_bwd: unsupported width d=%d", d);
-    if (M <= 0) return 0;
     const int G = 8 / cfg.wpr;
     const int grid = max(1, min((M + G - 1) / G, b200_num_sms() * 2));
-    const bool cs = colsum != nullptr;
     B200_REQUIRE(!cs || dx_in != nullptr, "ln_bwd: colsum needs dx_in");
     const int nacc = cs ? 3 : 2;
     const int smem = G * nacc * d * (int)sizeof(float);
@@ -321,9 +319,72 @@ extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, co
             B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(256), smem, st, (const bf16*)dy, x, mean, rstd, gamma, dx_in, dx_out, (bf16*)dx_bf16, partial, M));
         })
     }
+    *grid_out = grid;
+    return 0;
+}
+
+extern "C" int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* rstd,
+                           const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16,
+                           float* partial, float* dgamma, float* dbeta, float* colsum, int M, int d,
+                           int accumulate, cudaStream_t st) {
+    if (M <= 0) return 0;
+    const bool cs = colsum != nullptr;
+    int grid = 0;
+    if (int rc = ln_bwd_main(dy, x, mean, rstd, gamma, dx_in, dx_out, dx_bf16, partial, cs, M, d, &grid, st)) return rc;
+    const int nacc = cs ? 3 : 2;
     B200_CHECK_CUDA(b200_launch(ln_bwd_finalize_kernel, dim3(dim3((d + 31) / 32, nacc)), dim3(256), 0, st, partial, grid, nacc, d, dgamma, dbeta, colsum,
                                                                        accumulate));
     B200_RETURN_LAUNCH_STATUS("ln_bwd");
+}
+
+// Two-step form: the main kernel only (partial sums stay in `partial`), and ONE finalize launch for two LayerNorms of
+// the same (M, d) - the two of a transformer block - instead of one tiny launch each (25 per step, 10 us apiece).
+extern "C" int b200_ln_bwd_partial(const void* dy, const float* x, const float* mean, const float* rstd,
+                                   const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16,
+                                   float* partial, int with_colsum, int M, int d, cudaStream_t st) {
+    if (M <= 0) return 0;
+    int grid = 0;
+    if (int rc = ln_bwd_main(dy, x, mean, rstd, gamma, dx_in, dx_out, dx_bf16, partial, with_colsum != 0, M, d, &grid, st)) return rc;
+    B200_RETURN_LAUNCH_STATUS("ln_bwd_partial");
+}
+
+struct LnFin { const float* partial; float* o0; float* o1; float* o2; int nacc; };
+
+__global__ void __launch_bounds__(256) ln_bwd_finalize2_kernel(LnFin a, LnFin b, int nparts, int d, int accumulate) {
+    pdl_sync();
+    const LnFin f = blockIdx.z == 0 ? a : b;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    const int k = blockIdx.y;
+    if (k >= f.nacc) return;                                   // uniform per CTA
+    float* o = k == 0 ? f.o0 : (k == 1 ? f.o1 : f.o2);
+    __shared__ float red[8][33];
+    float s = 0.f;
+    if (c < d && o != nullptr) {
+        const float* p = f.partial + (size_t)k * d + c;
+        const size_t stride = (size_t)f.nacc * d;
+        for (int i = ty; i < nparts; i += 8) s += p[(size_t)i * stride];
+    }
+    red[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && c < d && o != nullptr) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t += red[j][tx];
+        o[c] = accumulate ? o[c] + t : t;
+    }
+}
+
+extern "C" int b200_ln_bwd_finalize2(const float* partial_a, float* dgamma_a, float* dbeta_a, float* colsum_a,
+                                     const float* partial_b, float* dgamma_b, float* dbeta_b, float* colsum_b, int M, int d,
+                                     int accumulate, cudaStream_t st) {
+    if (M <= 0) return 0;
+    const int nparts = b200_ln_bwd_nparts(M, d);
+    B200_REQUIRE(nparts > 0, "ln_bwd_finalize2: unsupported width d=%d", d);
+    LnFin a{partial_a, dgamma_a, dbeta_a, colsum_a, colsum_a ? 3 : 2};
+    LnFin b{partial_b, dgamma_b, dbeta_b, colsum_b, colsum_b ? 3 : 2};
+    B200_CHECK_CUDA(b200_launch(ln_bwd_finalize2_kernel, dim3((d + 31) / 32, 3, 2), dim3(256), 0, st, a, b, nparts, d, accumulate));
+    B200_RETURN_LAUNCH_STATUS("ln_bwd_finalize2");
 }
 
 // =============================================================================================

@@ -48,6 +48,11 @@ int b200_ln_bwd_nparts(int M, int d);
  * colsum (nullable) (+)= column sums of dx_in.  `partial` is scratch of
  * b200_ln_bwd_nparts(M,d) * (colsum ? 3 : 2) * d floats.  dx_in may alias dx_out. */
 int b200_ln_bwd(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16, float* partial, float* dgamma, float* dbeta, float* colsum, int M, int d, int accumulate, cudaStream_t st);
+/* Two-step form of the same backward: `_partial` runs the main kernel only and leaves the per-CTA partial sums in
+ * `partial` (same size as above; with_colsum selects the 3-accumulator layout); `_finalize2` then reduces the partials
+ * of TWO LayerNorms of the same (M, d) in one launch (pass colsum_x iff that LayerNorm ran with_colsum). */
+int b200_ln_bwd_partial(const void* dy, const float* x, const float* mean, const float* rstd, const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16, float* partial, int with_colsum, int M, int d, cudaStream_t st);
+int b200_ln_bwd_finalize2(const float* partial_a, float* dgamma_a, float* dbeta_a, float* colsum_a, const float* partial_b, float* dgamma_b, float* dbeta_b, float* colsum_b, int M, int d, int accumulate, cudaStream_t st);
 
 /* Same operation for callers that cannot allocate device memory (a host that gave the whole GPU to its own
  * arena; a loop that must not meet cudaMalloc's device-wide synchronisation).  This entry point has no

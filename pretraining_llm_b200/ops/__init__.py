@@ -191,6 +191,21 @@ def ln_bwd(dy, x, mean, rstd, gamma, dgamma, dbeta, *, dx_in=None, dx_out=None, 
     return dx_out
 
 
+def ln_bwd_partial(dy, x, mean, rstd, gamma, partial, *, dx_in=None, dx_out=None, dx_bf16=None, with_colsum: bool = False):
+    """Main kernel of ln_bwd only: dx (+ residual gradient, + bf16 copy); the parameter-gradient partial sums stay in
+    `partial` until ln_bwd_finalize2 reduces them (two LayerNorms per launch)."""
+    M, d = x.shape
+    _chk(lib.load().b200_ln_bwd_partial(_p(dy), _p(x), _p(mean), _p(rstd), _p(gamma), _p(dx_in), _p(dx_out), _p(dx_bf16),
+                                        _p(partial), int(with_colsum), M, d, _st()), "ln_bwd_partial")
+    return dx_out
+
+
+def ln_bwd_finalize2(M, d, partial_a, dgamma_a, dbeta_a, colsum_a, partial_b, dgamma_b, dbeta_b, colsum_b,
+                     accumulate: bool = False):
+    _chk(lib.load().b200_ln_bwd_finalize2(_p(partial_a), _p(dgamma_a), _p(dbeta_a), _p(colsum_a), _p(partial_b), _p(dgamma_b),
+                                          _p(dbeta_b), _p(colsum_b), M, d, int(accumulate), _st()), "ln_bwd_finalize2")
+
+
 def adamw(p, g, m, v, p_bf16, hyper):
     _chk(lib.load().b200_adamw(_p(p), _p(g), _p(m), _p(v), _p(p_bf16), _p(hyper), p.numel(), _st()), "adamw")
 

@@ -76,6 +76,7 @@ class Workspace:
             self.delta = e(B, H, T, dt=F32)
             self.dq_acc = torch.zeros(M, d, device=dev, dtype=F32) if ops.ATTN_BWD_IMPL != "tc" else None
             self.ln_partial = e(max(ops.ln_bwd_nparts(M, d), 1) * 3 * d, dt=F32)
+            self.ln_partial2 = torch.empty_like(self.ln_partial)     # second LayerNorm of a block (one finalize for both)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
 
 
@@ -253,17 +254,19 @@ class Engine:
             ops.colsum(w.dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
             ops.gemm(w.dh, w.h2[l], out=self.G(pre + "mlp.hidden.weight"), a_mn=True, b_mn=True, f32_mode=fm)
             ops.gemm(w.dh, self.W(pre + "mlp.hidden.weight"), out=w.dtmp, b_mn=True)
-            ops.ln_bwd(w.dtmp, w.resid_b[l], st2[0], st2[1], self.P(pre + "ln2.weight"), self.G(pre + "ln2.weight"),
-                       self.G(pre + "ln2.bias"), dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16,
-                       colsum_out=self.G(pre + "mlp.proj.bias"), partial=w.ln_partial, accumulate=accumulate)
+            # LayerNorm backward in two steps: the partial sums of ln2 and ln1 are reduced by ONE launch at the end of the block
+            ops.ln_bwd_partial(w.dtmp, w.resid_b[l], st2[0], st2[1], self.P(pre + "ln2.weight"), w.ln_partial,
+                               dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16, with_colsum=True)
             # ---- attention
             ops.attn_bwd(w.qkv[l], w.att[l], w.dx_bf16, w.lse[l], B, T, H, hs, dqkv=w.dqkv, delta=w.delta,
                          dq_acc=w.dq_acc)
             ops.gemm(w.dqkv, w.h1[l], out=self.G(pre + "attn.wqkv"), a_mn=True, b_mn=True, f32_mode=fm)
             ops.gemm(w.dqkv, self.W(pre + "attn.wqkv"), out=w.dtmp, b_mn=True)
-            ops.ln_bwd(w.dtmp, w.resid_a[l], st1[0], st1[1], self.P(pre + "ln1.weight"), self.G(pre + "ln1.weight"),
-                       self.G(pre + "ln1.bias"), dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16, partial=w.ln_partial,
-                       accumulate=accumulate)
+            ops.ln_bwd_partial(w.dtmp, w.resid_a[l], st1[0], st1[1], self.P(pre + "ln1.weight"), w.ln_partial2,
+                               dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16)
+            ops.ln_bwd_finalize2(w.M, lay.d, w.ln_partial, self.G(pre + "ln2.weight"), self.G(pre + "ln2.bias"),
+                                 self.G(pre + "mlp.proj.bias"), w.ln_partial2, self.G(pre + "ln1.weight"),
+                                 self.G(pre + "ln1.bias"), None, accumulate=accumulate)
             if dp is not None:
                 dp.bucket_ready(f"block{l}")
         ops.embed_bwd(w.idx, w.dx, self.G("token_embed.weight"), self.G("position_embed.weight")[:T],

@@ -290,6 +290,38 @@ def test_flash_attention_fwd_bwd(ops, hs, T, impl):
         assert err < 2e-2, (name, err.item())
 
 
+def test_ln_bwd_two_step_equals_one_step(ops):
+    """ln_bwd_partial x 2 + ln_bwd_finalize2 (one reduce launch for the two LayerNorms of a block) == two ln_bwd calls."""
+    torch.manual_seed(31)
+    M, d = 1000, 768
+    outs = []
+    for two_step in (False, True):
+        torch.manual_seed(32)
+        res = []
+        parts = [torch.empty(ops.ln_bwd_nparts(M, d) * 3 * d, device="cuda") for _ in range(2)]
+        grads = []
+        for k, cs in enumerate((True, False)):
+            x = torch.randn(M, d, device="cuda"); dy = _rand(M, d); g = torch.randn(d, device="cuda")
+            mean = x.mean(-1); rstd = (x.var(-1, unbiased=False) + 1e-5).rsqrt()
+            dxi = torch.randn(M, d, device="cuda")
+            dg, db, col = torch.zeros(d, device="cuda"), torch.zeros(d, device="cuda"), torch.zeros(d, device="cuda")
+            dxo, dxb = torch.empty(M, d, device="cuda"), torch.empty(M, d, device="cuda", dtype=BF16)
+            if two_step:
+                ops.ln_bwd_partial(dy, x, mean, rstd, g, parts[k], dx_in=dxi, dx_out=dxo, dx_bf16=dxb, with_colsum=cs)
+            else:
+                ops.ln_bwd(dy, x, mean, rstd, g, dg, db, dx_in=dxi, dx_out=dxo, dx_bf16=dxb,
+                           colsum_out=col if cs else None, partial=parts[k])
+            grads.append((dg, db, col if cs else None))
+            res += [dxo, dxb.float()]
+        if two_step:
+            ops.ln_bwd_finalize2(M, d, parts[0], *grads[0], parts[1], *grads[1])
+        for dg, db, col in grads:
+            res += [dg, db] + ([col] if col is not None else [])
+        outs.append(res)
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+
+
 @pytest.mark.parametrize("tiles", ["tc1", "tc2"])
 @pytest.mark.parametrize("hs", [64, 128])
 @pytest.mark.parametrize("T", [100, 384, 640, 1024, 2048])
