@@ -325,3 +325,32 @@ def test_grad_accumulation_equals_big_batch(tmp_path):
     for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
         # step-1 AdamW is ~ lr * g / (|g| + eps): only near-zero gradients may differ visibly
         assert (p - q).abs().max() < 1e-2 * 0.05 and ((p - q).abs() > 2e-6).float().mean() < 1e-3, n
+
+
+def test_layout_reference_roundtrip_property():
+    """Property test: for random shapes the flat store <-> reference state_dict translation is lossless, slots never
+    overlap, and the parameter count matches the closed form of SURVEY 2.6."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=25, deadline=None)
+    @given(H=st.sampled_from([1, 2, 3, 4]), hs=st.sampled_from([4, 8, 16]), ctx=st.integers(4, 40), V=st.integers(5, 300),
+           L=st.integers(1, 3), seed=st.integers(0, 2 ** 16))
+    def check(H, hs, ctx, V, L, seed):
+        d = H * hs
+        lay = ParamLayout(H, d, ctx, V, L)
+        assert lay.num_params() == L * (11 * d * d + 9 * d) + 2 * V * d + V + ctx * d + 2 * d
+        spans = sorted((s.offset, s.offset + s.numel) for s in lay.slots.values())
+        for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+            assert a1 <= b0
+        assert spans[-1][1] <= lay.total
+        g = torch.Generator().manual_seed(seed)
+        flat = torch.randn(lay.total, generator=g)
+        sd = lay.to_reference_state_dict(flat)
+        assert list(sd.keys()) == lay.reference_keys()
+        flat2 = torch.zeros(lay.total)
+        missing, unexpected = lay.from_reference_state_dict(flat2, sd, True)
+        assert not missing and not unexpected
+        for n in lay.slots:
+            assert torch.equal(lay.view(flat, n), lay.view(flat2, n)), n
+
+    check()

@@ -77,3 +77,36 @@ def test_two_process_gloo_training_keeps_replicas_identical(tmp_path):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     assert "OK" in r.stdout
     assert os.path.exists(tmp_path / "m.pt")
+
+
+def test_bucket_plan_property_random_models():
+    """Property test over random model shapes / world sizes / vocab-parallel: every element of every bucket has exactly one
+    owner, slices are 16-byte aligned, and the per-slot table is consistent with the layout."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=40, deadline=None)
+    @given(heads=st.sampled_from([1, 2, 4, 12]), hs=st.sampled_from([8, 64, 128]), layers=st.integers(1, 5),
+           ctx=st.sampled_from([16, 100, 1024]), vocab=st.sampled_from([257, 1000, 50304]),
+           world=st.sampled_from([1, 2, 4, 8]), vp=st.booleans())
+    def check(heads, hs, layers, ctx, vocab, world, vp):
+        lay = ParamLayout(heads, heads * hs, ctx, vocab, layers)
+        plans = plan_buckets(lay, world, vocab_parallel=vp)
+        assert plans[0].name == "head" and plans[-1].name == "embed" and len(plans) == layers + 2
+        covered = 0
+        for p in plans:
+            assert p.start % 4 == 0 and p.chunk % 4 == 0
+            prev_end = p.start
+            for r in range(world):
+                s, c = p.slice_of(r)
+                assert s == min(p.start + r * p.chunk, p.end) and c >= 0 and c % 4 == 0
+                assert s >= prev_end or c == 0
+                prev_end = max(prev_end, s + c)
+                covered += c
+            assert prev_end == p.end
+            assert len(p.slot_end) == len(p.slot_fp32) and p.slot_end[-1] == p.end
+        excluded = 0
+        if vp:   # the LM head leaves the head bucket (owned by vocabulary slice instead)
+            excluded = lay.buckets()[0][2] - lay.slots["lm_head.weight"].offset
+        assert covered == lay.total - excluded
+
+    check()
