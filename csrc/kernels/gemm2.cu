@@ -242,6 +242,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 }
                 for (; i < nvec; i += stride) dv[i] = ldg_stream_u4(sv + i);
                 __threadfence();
+                // named barriers of this kernel: 1 (+2 when there are two epilogue groups) = epilogue groups, 3 = bias staging,
+                // 2 = these gather warps (the AG variant has ONE epilogue group, so id 2 is free here)
                 asm volatile("bar.sync 2, 128;" ::: "memory");
                 if (gt == 0) {
                     const unsigned prev = atomicAdd(ag.counters + src_rank, 1u);
