@@ -181,9 +181,13 @@ def run_reference_bench(args, root: str, m: dict, lr: float) -> None:
             "dtype": "bf16 autocast", "data": "synthetic random tokens, random-init weights",
             "config": {"model": f"{args.model}-shaped decoder {m['n_blocks']}L d={m['n_embed']} H={m['n_head']} "
                                 f"seq={T} vocab={V}", "global_batch": B * world, "seq_len": T,
-                       "parallelism": f"dp{world}", "torch_compile": compiled,
-                       "ddp": "torch DDP/NCCL, sync every step" if world > 1 else "none",
-                       "reference_root": root},
+                       "parallelism": f"dp{world}",
+                       "optimizer": "AdamW (torch defaults), every step",
+                       "l2": "no flush: per-step working set (activations + weights + optimizer state, >4 GB) "
+                             "is far larger than the 126 MB L2"},
+            "arm_details": {"torch_compile": compiled,
+                            "ddp": "torch DDP/NCCL, sync every step" if world > 1 else "none",
+                            "reference_root": root},
             "final_loss": final_loss, "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": 0,
         }), flush=True)
     if world > 1:

@@ -95,14 +95,21 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
     pdl_sync();
     const int epoch = *epoch_dev;   // device-resident step counter: the same CUDA graph serves every step
     // ---- 1. handshake: every rank has finished writing this bucket's gradients
+    __shared__ int s_peers_ok;
     if (threadIdx.x == 0) {
         if (blockIdx.x == 0) {
             __threadfence_system();
             for (int r = 0; r < W; ++r) st_release_sys(P.sig[r] + rank * nb + bucket, epoch);
         }
-        for (int r = 0; r < W; ++r) wait_flag(P.sig[rank] + r * nb + bucket, epoch, err);
+        bool ok = true;
+        for (int r = 0; r < W; ++r) ok = wait_flag(P.sig[rank] + r * nb + bucket, epoch, err) && ok;
+        s_peers_ok = ok ? 1 : 0;
     }
     __syncthreads();
+    // A peer never showed up (dead or diverged rank): its gradients are not there.  Leave the weights, the moments and
+    // the done flag untouched - the error flag is up, dp_wait_done times out on the peers, and the host raises at its
+    // next check_errors() - instead of applying an update built from incomplete sums.
+    if (!s_peers_ok) return;
 
     const float decay = hyper[0], b2 = hyper[1], w1 = hyper[2], w2 = hyper[3], step_size = hyper[4],
                 bc2s = hyper[5], eps = hyper[6], gs = hyper[7];

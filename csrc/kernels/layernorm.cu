@@ -413,6 +413,9 @@ extern "C" int b200_ln_bwd_finalize2(const float* partial_a, float* dgamma_a, fl
 #define LN_BWD_STATIC_FLOATS (296 * 3 * 2048)
 static __device__ __align__(256) float g_ln_bwd_static_scratch[LN_BWD_STATIC_FLOATS];
 
+// Host threads: the per-device cache below is written without a lock.  Two threads that make the FIRST call on the same
+// device at the same time both look the symbol up and store the same value (a benign same-value race on an aligned
+// pointer); the array itself is what concurrent callers must not share (see above).
 static float* ln_bwd_static_address() {
     static float* addr[64] = {nullptr};
     int dev = 0;
@@ -437,6 +440,7 @@ extern "C" long long b200_ln_bwd_static_capacity() { return (long long)LN_BWD_ST
 extern "C" int b200_ln_bwd_static(const void* dy, const float* x, const float* mean, const float* rstd,
                                   const float* gamma, const float* dx_in, float* dx_out, void* dx_bf16, float* dgamma,
                                   float* dbeta, float* colsum, int M, int d, int accumulate, cudaStream_t st) {
+    if (M <= 0) return 0;                       // nothing to do (same early-out as b200_ln_bwd_partial)
     const int nparts = b200_ln_bwd_nparts(M, d);
     B200_REQUIRE(nparts > 0, "ln_bwd_static: unsupported width d=%d", d);
     const long long need = (long long)nparts * (colsum != nullptr ? 3 : 2) * d;

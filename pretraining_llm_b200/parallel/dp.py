@@ -119,8 +119,6 @@ class DataParallel:
         for _, cnt in self.owned:
             self.opt_off.append(off)
             off += cnt
-        if eng.exp_avg is not None:
-            self.state_loaded()
         # sharded-weight ("zero") mode: per-layer, per-source-rank "chunk gathered" flags + arrival counters, and the
         # weight version they are compared against (bumped after every optimizer step)
         self.zero = mode == "zero"
@@ -140,6 +138,8 @@ class DataParallel:
         if vocab_parallel and self.world > 1:
             from .vp import VocabParallelHead
             self.vp = VocabParallelHead(eng, self)
+        if eng.exp_avg is not None:        # moments loaded before the ranks were attached (resume): keep the owned slices
+            self.state_loaded()
         dist.barrier()
         torch.cuda.synchronize()
 
@@ -273,3 +273,4 @@ class DataParallel:
         for o, (s, c) in zip(self.opt_off, self.owned):
             self.m[o:o + c] = eng.exp_avg[s:s + c]
             self.v[o:o + c] = eng.exp_avg_sq[s:s + c]
+        eng.release_full_opt_state()

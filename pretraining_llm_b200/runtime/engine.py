@@ -134,6 +134,12 @@ class Engine:
             self.exp_avg = torch.zeros_like(self.flat)
             self.exp_avg_sq = torch.zeros_like(self.flat)
 
+    def release_full_opt_state(self) -> None:
+        """Drop the full-size moment buffers (8 B/parameter).  With data parallelism attached they are only
+        materialised for a checkpoint or a resume; the live moments are the owner slices in dp.m / dp.v."""
+        self.exp_avg = None
+        self.exp_avg_sq = None
+
     def workspace(self, B: int, T: int, train: bool) -> Workspace:
         key = (B, T, train)
         w = self.ws.get(key)
@@ -291,12 +297,12 @@ class Engine:
 
     def optimizer_step(self) -> None:
         """Fused AdamW over the whole flat buffer (fp32 masters + bf16 shadow) using staged scalars."""
-        self.ensure_opt_state()
         if self.dp is not None:
             self.dp.reduce_and_step()
             if self.dp.vp is not None:
                 self.dp.vp.step()
         else:
+            self.ensure_opt_state()
             ops.adamw(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.wb, self.hyper)
         # our kernel wrote the masters and the shadow together: keep them marked in sync
         self._wb_version = self.flat._version
@@ -314,7 +320,8 @@ class Engine:
         B, T = idx.shape
         w = self.workspace(B, T, True)
         self.ensure_grad()
-        self.ensure_opt_state()
+        if self.dp is None:
+            self.ensure_opt_state()        # with data parallelism the moments live sharded in dp.m / dp.v
         self.sync_weights()
         w.idx.copy_(idx, non_blocking=True)
         w.tgt.copy_(targets.reshape(B, T), non_blocking=True)
@@ -349,7 +356,8 @@ class Engine:
             targets = targets.contiguous().long()
         if not grad_mode:
             _, logits, loss = self.forward(idx, targets, train=False)
-            return logits, (loss.clone() if loss is not None else None)
+            # the workspace is reused by the next call of the same shape: hand out copies, not views
+            return logits.clone(), (loss.clone() if loss is not None else None)
         params = [p for _, p in self.model.named_parameters()]
         loss, logits = _EngineLoss.apply(self, idx, targets, *params)
         return logits, loss
@@ -372,6 +380,7 @@ class _EngineLoss(torch.autograd.Function):
     def forward(ctx, eng: Engine, idx, targets, *params):
         w, logits, loss = eng.forward(idx, targets, train=True)
         ctx.eng, ctx.w = eng, w
+        logits = logits.clone()       # backward turns the workspace logits into dlogits in place
         ctx.mark_non_differentiable(logits)
         return loss.clone(), logits
 
@@ -380,4 +389,8 @@ class _EngineLoss(torch.autograd.Function):
         eng: Engine = ctx.eng
         eng.backward(ctx.w, grad_scale=float(gloss))
         names = [n for n, _ in eng.model.named_parameters()]
-        return (None, None, None) + tuple(eng.layout.view(eng.grad, n) for n in names)
+        # Copies, not views of the shared gradient buffer: autograd's AccumulateGrad keeps the tensor it is given as
+        # p.grad, and a second backward() without zero_grad (ordinary torch gradient accumulation) would first
+        # overwrite the buffer and then add it to itself.  One clone of the flat buffer, sliced per parameter.
+        g = eng.grad.clone()
+        return (None, None, None) + tuple(eng.layout.view(g, n) for n in names)

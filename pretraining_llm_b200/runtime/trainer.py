@@ -44,13 +44,18 @@ class Trainer:
         self.train_iterator = train_iterator
         self.val_iterator = val_iterator
         self.dist = dist_ctx or bootstrap.DistContext()
+        # The hand-written kernels compute in bf16 (fp32 statistics / masters).  dtype="float32" and "float16" are the
+        # reference's other two branches (train_transformer.py:41,69,92-93): they run its recipe in plain PyTorch -
+        # fp32 without autocast, fp16 under autocast with a GradScaler - instead of being silently computed in bf16.
+        dtype = self.config.get("dtype", "bfloat16")
+        if dtype != "bfloat16" and hasattr(model, "use_native"):
+            model.use_native = False
         self.native = bool(getattr(model, "_native_ok", lambda: False)())
         self.optimizer = optimizer
         if not self.native and optimizer is None:
             self.optimizer = torch.optim.AdamW(model.parameters(), lr=self.config["t_lr"])
-        # fp16 would need loss scaling (the reference keeps a GradScaler for it); bf16/fp32 do not
-        if self.config["dtype"] == "float16":
-            raise NotImplementedError("float16 training is not supported; use bfloat16 (the reference default)")
+        on_cuda = next(model.parameters()).is_cuda
+        self.scaler = torch.amp.GradScaler("cuda", enabled=(dtype == "float16" and on_cuda and not self.native))
         self.step = 0
         self.tokens_per_step = None
         self.log_file = open(self.config["log_jsonl"], "a") if self.config.get("log_jsonl") and self.dist.master else None
@@ -65,8 +70,10 @@ class Trainer:
 
     def _autocast(self):
         dev = "cuda" if next(self.model.parameters()).is_cuda else "cpu"
-        enabled = self.config["dtype"] == "bfloat16"
-        return torch.autocast(device_type=dev, dtype=torch.bfloat16, enabled=enabled)
+        dtype = self.config["dtype"]
+        if dtype == "float16" and dev == "cuda":
+            return torch.autocast(device_type=dev, dtype=torch.float16)
+        return torch.autocast(device_type=dev, dtype=torch.bfloat16, enabled=dtype == "bfloat16")
 
     @torch.no_grad()
     def _evaluate(self) -> float:
@@ -98,6 +105,9 @@ class Trainer:
             if accum == 1:
                 return eng.train_step(xb, yb, lr, use_graph=self.config.get("use_cuda_graph", True))
             loss_acc = None
+            # the fused reduce+AdamW kernels of the last micro-step read the staged scalars while backward is still
+            # running: stage them BEFORE the loop (same order as Engine.train_step)
+            eng.set_hyper(lr)
             if eng.dp is not None:
                 eng.dp.begin_step()
             for k in range(accum):
@@ -106,7 +116,6 @@ class Trainer:
                 w, _, loss = eng.forward(xb.contiguous(), yb.contiguous(), train=True)
                 eng.backward(w, grad_scale=1.0 / accum, accumulate=k > 0, dp_sync=(k == accum - 1))
                 loss_acc = loss.clone() if loss_acc is None else loss_acc + loss
-            eng.set_hyper(lr)
             eng.optimizer_step()
             return loss_acc / accum
         for g in self.optimizer.param_groups:
@@ -117,10 +126,11 @@ class Trainer:
                 xb, yb = next(self.train_iterator)
             with self._autocast():
                 _, loss = self.model(xb, yb)
-            (loss / accum).backward()
+            self.scaler.scale(loss / accum).backward()
             loss_acc = loss.detach() if loss_acc is None else loss_acc + loss.detach()
         self.dist.all_reduce_grads(self.model)
-        self.optimizer.step()
+        self.scaler.step(self.optimizer)          # plain optimizer.step() unless fp16 scaling is on
+        self.scaler.update()
         self.optimizer.zero_grad(set_to_none=True)
         return loss_acc / accum
 
@@ -129,15 +139,20 @@ class Trainer:
         """{'model_state_dict', 'optimizer_state_dict'} in the reference's layout
         (train_transformer.py:106-109) plus 'trainer_state' for resuming."""
         model = self.model
+        if self.native and model.engine.dp is not None:
+            # each rank holds current fp32 masters only for the slices it owns: complete them (and the moments)
+            # BEFORE the state_dict is cloned out of the flat buffer
+            model.engine.dp.check_errors()
+            model.engine.dp.gather_full_state()
         sd = model.state_dict()
         lr = self._get_lr(max(self.step - 1, 0))
         if self.native:
             eng = model.engine
-            if eng.dp is not None:
-                eng.dp.gather_full_state()
             eng.ensure_opt_state()
             osd = model.layout.to_reference_optimizer_state(eng.exp_avg, eng.exp_avg_sq, eng.step_count, lr,
                                                             eng.betas, eng.eps, eng.weight_decay)
+            if eng.dp is not None:
+                eng.release_full_opt_state()      # the sharded dp.m / dp.v are the live copies
         else:
             osd = self._reference_optimizer_state()
         return {"model_state_dict": sd, "optimizer_state_dict": osd,
@@ -194,6 +209,12 @@ class Trainer:
         if ts:
             self.step = int(ts["step"])
 
+    def _mfu(self, tokens_per_s: float, T: int) -> float:
+        """Model-FLOP utilisation of the whole job against the measured bf16 tensor peak (utils/flops.py)."""
+        from ..utils.flops import mfu
+        m = self.model
+        return mfu(tokens_per_s, m.N_BLOCKS, m.n_embed, m.vocab_size, T, self.dist.world)
+
     # ------------------------------------------------------------------ main loop
     def train(self) -> None:
         cfg = self.config
@@ -225,16 +246,21 @@ class Trainer:
                 else:
                     dt_dev = time.time() - t0
                 t1 = time.time()
+                if self.native and self.model.engine.dp is not None:
+                    self.model.engine.dp.check_errors()     # a peer time-out must stop the run, not train on garbage
                 val_loss = self._evaluate()
                 train_loss = float(self.dist.all_reduce_mean(loss.detach().float()).item())
                 toks = self.tokens_per_step * steps_in_window / max(dt_dev, 1e-9)
+                util = self._mfu(toks, xb.shape[-1]) if cuda else float("nan")
                 if self.dist.master:
                     # first five fields: the reference's line (train_transformer.py:101)
                     print(f"Step {step}: Train Loss={train_loss:.4f}, Val Loss={val_loss:.4f}, LR={lr:.2e}, "
-                          f"Time={(t1 - t0) * 1000:.2f}ms, tokens/s={toks:,.0f}", flush=True)
+                          f"Time={(t1 - t0) * 1000:.2f}ms, tokens/s={toks:,.0f}"
+                          + (f", MFU={util * 100:.1f}%" if cuda else ""), flush=True)
                     if self.log_file:
                         self.log_file.write(json.dumps({"step": step, "train_loss": train_loss, "val_loss": val_loss,
-                                                        "lr": lr, "tokens_per_s": toks, "device_s": dt_dev}) + "\n")
+                                                        "lr": lr, "tokens_per_s": toks, "device_s": dt_dev,
+                                                        "mfu": util}) + "\n")
                         self.log_file.flush()
                 t0 = time.time()
                 steps_in_window = 0

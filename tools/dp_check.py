@@ -17,8 +17,15 @@ from pretraining_llm_b200.models import Transformer  # noqa: E402
 from pretraining_llm_b200.parallel.bootstrap import init_distributed  # noqa: E402
 from pretraining_llm_b200.parallel.dp import DataParallel  # noqa: E402
 
-CFG = dict(n_head=4, n_embed=256, context_length=128, vocab_size=1000)
-L, B, T, STEPS, LR = 3, 4, 128, 5, 1e-3
+if os.environ.get("DP_SHAPE", "tiny") == "small":      # the benchmark's layer shape: d=768, T=1024, ragged vocabulary
+    CFG = dict(n_head=12, n_embed=768, context_length=1024, vocab_size=50304)
+    L, B, T, STEPS, LR = 2, 4, 1024, 4, 5e-4
+elif os.environ.get("DP_SHAPE") == "1.3b-layer":       # the 1.3B layer shape (hs=128, d=2048, T=2048), two layers
+    CFG = dict(n_head=16, n_embed=2048, context_length=2048, vocab_size=50304)
+    L, B, T, STEPS, LR = 2, 2, 2048, 3, 5e-4
+else:
+    CFG = dict(n_head=4, n_embed=256, context_length=128, vocab_size=1000)
+    L, B, T, STEPS, LR = 3, 4, 128, 5, 1e-3
 
 
 def batches(rank, step):
@@ -42,7 +49,7 @@ def main():
     losses = []
     for step in range(STEPS):
         x, y = batches(r, step)
-        losses.append(eng.train_step(x, y, LR))
+        losses.append(eng.train_step(x, y, LR).clone())   # the return value is a view of the workspace loss
         if oracle is not None:
             xs, ys = zip(*[batches(q, step) for q in range(W)])
             oracle.engine.train_step(torch.cat(xs), torch.cat(ys), LR, use_graph=False)
@@ -73,11 +80,13 @@ def main():
         print(f"world {W}: max|dW| {dw:.3e}  max|dm| {dm:.3e}  max|dv| {dv:.3e}  replicas_identical {ok}  "
               f"losses {[round(float(v), 4) for v in mean_loss]}")
         assert ok, "bf16 weight replicas differ between ranks"
-        # The moments are linear in the gradients and must agree tightly.  A weight can legitimately differ by up to
-        # ~lr per step where Adam divides a rounding-level gradient by a rounding-level sqrt(v) (sign flips between two
-        # summation orders), so the weights are held to a bound on the MEAN difference plus the hard per-step cap.
+        # The moments are linear in the gradients and must agree tightly (observed 1e-5: bound 10x that).  A single
+        # weight can legitimately differ by ~lr per step where Adam divides a rounding-level gradient by a rounding-level
+        # sqrt(v) (sign flips between two summation orders), so the max is not informative; the MEAN difference is,
+        # and it is held to 2e-3 of the distance Adam can move a weight in STEPS steps (printed for the record).
         dw_mean = (eng.flat - o.flat).abs().mean().item()
-        assert dm < 1e-3 and dw_mean < 0.02 * LR * STEPS and dw <= 1.5 * LR * STEPS, (dw, dw_mean, dm)
+        print(f"mean|dW| {dw_mean:.3e} = {dw_mean / (LR * STEPS):.2e} of lr*steps")
+        assert dm < 1e-4 and dw_mean < 2e-3 * LR * STEPS, (dw, dw_mean, dm)
         print("DP_CHECK_OK")
     ctx.shutdown()
 
