@@ -154,6 +154,23 @@ int b200_ipc_free(void* ptr);
 int b200_ipc_export(void* ptr, void* h_handle_out);
 int b200_ipc_import(const void* h_handle, void** ptr_out);
 int b200_ipc_close(void* ptr);
+/* Symmetric heap on the virtual-memory-management API + NVSwitch multicast objects (csrc/comm/vmm.cu).
+ * query: out[5] = {VMM supported, POSIX-fd handles supported, multicast supported, allocation granularity,
+ * multicast granularity for `world` devices}.  create: cuMemCreate on the current device (+ an fd of THIS process
+ * to hand to the peers over a unix socket); import: fd -> handle; map: reserve + map + read/write access for the
+ * current device (local memory, a peer's memory and a multicast object alike).  Multicast: one rank creates the
+ * object, every rank adds its device, then - once ALL have - binds its local allocation and maps the object:
+ * stores to that mapping (multimem.st) land in every rank's copy, multimem.ld_reduce returns the switch-reduced sum. */
+int b200_vmm_query(long long* out, int world);
+int b200_vmm_create(long long bytes, unsigned long long* handle_out, int* fd_out);
+int b200_vmm_import(int fd, unsigned long long* handle_out);
+int b200_vmm_map(unsigned long long handle, long long bytes, void** ptr_out);
+int b200_vmm_unmap(void* ptr, long long bytes);
+int b200_vmm_release(unsigned long long handle);
+int b200_vmm_close_fd(int fd);
+int b200_mc_create(long long bytes, int world, unsigned long long* handle_out, int* fd_out);
+int b200_mc_add_device(unsigned long long mc_handle);
+int b200_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, long long bytes);
 /* Fused per-bucket gradient reduce-scatter (P2P loads) + scale + AdamW on the owned 1/W slice
  * [start, start+n) + all-gather of the updated weights (P2P stores of bf16, and fp32 where flagged).
  * h_grad/h_wb/h_flat/h_sig: host arrays of `world` peer-mapped device pointers (own rank included);

@@ -14,6 +14,7 @@ from typing import Optional
 import torch
 
 from . import lib
+from ..utils import nvtx as _nvtx
 
 BF16 = torch.bfloat16
 F32 = torch.float32
@@ -37,6 +38,8 @@ def _chk(rc: int, what: str) -> None:
     if rc != 0:
         lib.check(rc, what)
     LAUNCHES += _KERNELS_PER_CALL.get(what, 1)
+    if _nvtx.ENABLED:              # B200_NVTX=1: one NVTX marker per launch, named after the kernel family
+        torch.cuda.nvtx.mark(what)
 
 
 # ------------------------------------------------------------------------------------------ GEMM

@@ -31,6 +31,7 @@ from typing import Dict, Optional, Tuple
 import torch
 
 from .. import ops
+from ..utils import nvtx
 
 BF16, F32 = torch.bfloat16, torch.float32
 
@@ -342,9 +343,12 @@ class Engine:
     def _step_body(self, w: Workspace) -> None:
         if self.dp is not None:
             self.dp.begin_step()
-        self._forward_ws(w, True)
-        self.backward(w)
-        self.optimizer_step()
+        with nvtx.range("forward"):
+            self._forward_ws(w, True)
+        with nvtx.range("backward"):
+            self.backward(w)
+        with nvtx.range("optimizer"):
+            self.optimizer_step()
 
     # ------------------------------------------------------------------ nn.Module facade path
     def module_forward(self, idx: torch.Tensor, targets: Optional[torch.Tensor]):
