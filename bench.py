@@ -136,13 +136,15 @@ def dp_self_check(eng, m, B, T, V, dev, rank, world):
     except RuntimeError:
         out["err_flag"] = 1
     eng.dp.gather_full_state()                      # collective: fp32 masters complete on every rank
-    flat = eng.flat[:eng.layout.total]
+    flat = eng.flat[:eng.layout.total].clone()
     h = flat.view(torch.int32).to(torch.int64).sum()
     hmin, hmax = h.clone(), h.clone()
     dist.all_reduce(hmin, op=dist.ReduceOp.MIN)
     dist.all_reduce(hmax, op=dist.ReduceOp.MAX)
     out["replicas_identical"] = bool(hmin.item() == hmax.item())
     eng.release_full_opt_state()
+    if hasattr(eng.dp, "release_full"):
+        eng.dp.release_full()                        # sharded mode: back to shards only
     ok = torch.zeros(1, device=dev)
     if rank == 0:
         torch.manual_seed(1234)
@@ -200,10 +202,17 @@ def run_ours(args):
     eng = model.engine
     mode = "single"
     if world > 1:
-        from pretraining_llm_b200.parallel.dp import DataParallel
+        from pretraining_llm_b200.parallel import make_data_parallel
         ctx = DistContext(rank=rank, local_rank=local, world=world, device=dev)
-        eng.dp = DataParallel(eng, ctx, mode=args.dp_mode, vocab_parallel=args.vocab_parallel)
-        mode = "fused-allreduce-adamw" if args.dp_mode == "ddp" else "zero: fused reduce-scatter+adamw, all-gather fused in GEMMs"
+        make_data_parallel(eng, ctx, args.dp_mode, args.vocab_parallel)
+        mode = "fused-allreduce-adamw" if args.dp_mode == "ddp" else "zero: sharded params/grads/optimizer, fused reduce-scatter+adamw, all-gather fused in GEMMs"
+    comm_info = None
+    if eng.dp is not None:
+        sym = getattr(eng.dp, "sym_grad", None) or eng.dp.sym_gwin[0]
+        comm_info = {"symmetric_heap": sym.kind, "multimem": bool(eng.dp.multicast)}
+        if hasattr(eng.dp, "memory_report"):
+            comm_info["param_grad_opt_GiB_per_rank"] = {k: round(v, 3) for k, v in eng.dp.memory_report().items()}
+            comm_info["torch_allocated_GiB_after_setup"] = round(torch.cuda.memory_allocated() / 2 ** 30, 3)
     batches = synthetic_batches(4, B, T, V, dev, seed=100 + rank)
     use_graph = not args.no_graph
 
@@ -268,7 +277,7 @@ def run_ours(args):
                              "is far larger than the 126 MB L2"},
             # arm-specific details live OUTSIDE `config` so that both arms report key-identical configs
             "arm_details": {"dp_mode": mode, "cuda_graph": use_graph, "vocab_parallel": bool(args.vocab_parallel),
-                            "pdl": os.environ.get("B200_PDL", "default")},
+                            "pdl": os.environ.get("B200_PDL", "default"), "comm": comm_info},
             "final_loss": final_loss, "clocks": clk, "e2e": e2e, "gpu_launches": per_step * args.steps,
             "gpu_launches_per_step": per_step, "dp_check": dp_check,
             "mfu_of_measured_sustained": _mfu(value, m, T, world),

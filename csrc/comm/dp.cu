@@ -17,8 +17,8 @@
 // (reference scripts/train_transformer.py:122-123,92).
 #include "b200llm.h"
 #include "common.cuh"
+#include "comm.cuh"
 
-#define DP_MAX_WORLD 8
 #define DP_MAX_SLOTS 16
 
 // ---------------------------------------------------------------------------------------------
@@ -51,35 +51,14 @@ extern "C" int b200_ipc_close(void* ptr) {
     return 0;
 }
 
-// ---------------------------------------------------------------------------------------------
-// flags
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_release_sys(int* p, int v) {
-    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ int ld_acquire_sys(const int* p) {
-    int v;
-    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-// spin until *p >= target; gives up after ~20 s and raises the error flag instead of hanging
-__device__ __forceinline__ bool wait_flag(const int* p, int target, int* err) {
-    const long long t0 = clock64();
-    while (ld_acquire_sys(p) < target) {
-        __nanosleep(64);
-        if (clock64() - t0 > 40000000000ll) {
-            if (err) *err = 1;
-            return false;
-        }
-    }
-    return true;
-}
-
 struct DpPeers {
     float* grad[DP_MAX_WORLD];   // full flat fp32 gradient buffer of every rank
     bf16* wb[DP_MAX_WORLD];      // full flat bf16 shadow weights of every rank
     float* flat[DP_MAX_WORLD];   // full flat fp32 master weights of every rank
     int* sig[DP_MAX_WORLD];      // signal pad of every rank: [2][W][NB] ints (ready | done)
+    float* mc_grad;              // multicast mappings of the three buffers (MC kernels only; null otherwise)
+    bf16* mc_wb;
+    float* mc_flat;
 };
 struct DpSlots {                 // slots of the bucket: element END offsets (ascending) + "peers need fp32"
     long long end[DP_MAX_SLOTS];
@@ -87,11 +66,14 @@ struct DpSlots {                 // slots of the bucket: element END offsets (as
     int n;
 };
 
-template <int W>
+// MC = true: the buffers are bound into NVSwitch multicast objects.  The pull is ONE multimem.ld_reduce per 16 bytes
+// (the switch adds the W copies) instead of W peer loads, and each push is ONE multimem.st the switch replicates
+// instead of W peer stores: NVLink carries 1/W-th of the reduce traffic into this GPU and one copy out of it.
+template <int W, bool MC>
 __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int rank, int bucket, int nb, const int* __restrict__ epoch_dev,
                                                               long long start, long long n, float* __restrict__ m,
                                                               float* __restrict__ v, const float* __restrict__ hyper,
-                                                              DpSlots slots, unsigned int* cta_counter, int* err, int zero_mode) {
+                                                              DpSlots slots, unsigned int* cta_counter, int* err) {
     pdl_sync();
     const int epoch = *epoch_dev;   // device-resident step counter: the same CUDA graph serves every step
     // ---- 1. handshake: every rank has finished writing this bucket's gradients
@@ -119,12 +101,17 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
          i += (long long)gridDim.x * blockDim.x) {
         const long long e = start + i * 4;
         // ---- 2. pull + reduce (all W loads in flight before the first add)
-        float4 g[W];
+        float4 s;
+        if (MC) {
+            s = multimem_ld_reduce_add_f4(P.mc_grad + e);
+        } else {
+            float4 g[W];
 #pragma unroll
-        for (int r = 0; r < W; ++r) g[r] = ldg_stream_f4(reinterpret_cast<const float4*>(P.grad[r] + e));
-        float4 s = g[0];
+            for (int r = 0; r < W; ++r) g[r] = ldg_stream_f4(reinterpret_cast<const float4*>(P.grad[r] + e));
+            s = g[0];
 #pragma unroll
-        for (int r = 1; r < W; ++r) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+            for (int r = 1; r < W; ++r) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+        }
         // ---- 3. AdamW on the owned slice (same operation order as adamw.cu)
         float4 pv = *reinterpret_cast<float4*>(p_master + e);
         float4 mv = reinterpret_cast<float4*>(m)[i];
@@ -149,9 +136,9 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
         }
         const uint2 pb = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
         *reinterpret_cast<float4*>(p_master + e) = pv;
-        if (zero_mode && !need32) {
-            // sharded weights: matrices stay with their owner; consumers pull them inside the forward GEMM
-            *reinterpret_cast<uint2*>(P.wb[rank] + e) = pb;
+        if (MC) {
+            multimem_st_bf16x4(P.mc_wb + e, pb);
+            if (need32) multimem_st_f4(P.mc_flat + e, pv);
         } else {
 #pragma unroll
             for (int r = 0; r < W; ++r) {
@@ -184,7 +171,7 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
                                     int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start,
                                     long long n, float* m, float* v, const float* hyper, const long long* h_slot_end,
                                     const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas,
-                                    int zero_mode, cudaStream_t st) {
+                                    void* mc_grad, void* mc_wb, void* mc_flat, cudaStream_t st) {
     B200_REQUIRE(world >= 1 && world <= DP_MAX_WORLD, "dp: world size %d not supported (max %d)", world, DP_MAX_WORLD);
     B200_REQUIRE(n_slots <= DP_MAX_SLOTS, "dp: too many slots in one bucket");
     B200_REQUIRE(n % 4 == 0 && start % 4 == 0, "dp: slice must be 16-byte aligned");
@@ -194,6 +181,8 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
     for (int r = 0; r < world; ++r) {
         P.grad[r] = (float*)h_grad[r]; P.wb[r] = (bf16*)h_wb[r]; P.flat[r] = (float*)h_flat[r]; P.sig[r] = (int*)h_sig[r];
     }
+    const bool mc = mc_grad != nullptr && mc_wb != nullptr && mc_flat != nullptr && world > 1;
+    P.mc_grad = (float*)mc_grad; P.mc_wb = (bf16*)mc_wb; P.mc_flat = (float*)mc_flat;
     DpSlots S;
     memset(&S, 0, sizeof(S));
     S.n = n_slots;
@@ -209,8 +198,12 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
         if (threads < 32 || threads > 512 || threads % 32) threads = 512;
     }
 #define DP_LAUNCH(W_)                                                                                            \
-    B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
-                                                     (unsigned int*)cta_counter, err, zero_mode))
+    if (mc)                                                                                                      \
+        B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_, true>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
+                                    (unsigned int*)cta_counter, err));                               \
+    else                                                                                                         \
+        B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_, false>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
+                                    (unsigned int*)cta_counter, err))
     switch (world) {
         case 1: DP_LAUNCH(1); break;
         case 2: DP_LAUNCH(2); break;

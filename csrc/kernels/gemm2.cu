@@ -22,6 +22,7 @@ namespace {
 
 using gemm::Params;
 using gemm::AgParams;
+using gemm::AgJob;
 using gemm::EPI_BUF_BYTES;
 constexpr int BK = 64;
 constexpr int A_BYTES = 128 * BK * 2;   // this CTA's 128 rows of A
@@ -105,22 +106,29 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             int stage = 0;
             uint32_t phase = 0;
             unsigned ready_mask = 0;                    // chunks already seen valid (AG)
-            const int ag_epoch = (AG && ag.flags != nullptr) ? __shfl_sync(0xffffffffu, *ag.epoch, 0) : 0;
+            const int ag_gen = (AG && ag.wait_flags != nullptr) ? __shfl_sync(0xffffffffu, *ag.gen, 0) : 0;
             for (int u = pair; u < nunits; u += npairs) {
                 const int tile = u % ntiles, split = u / ntiles;
                 const int m0 = (tile % p.num_m) * 256 + (int)rank * 128;
                 const int n0 = (((tile / p.num_m) + p.n_shift) % p.num_n) * BN + (int)rank * (BN / 2);
                 const int kb0 = split * p.kb_per_split;
                 const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
-                if (AG && ag.flags != nullptr && !B_MN) {
-                    // rows [n0, n0 + BN/2) of the [N, K] weight -> flat element range -> owning chunks
+                if (AG && ag.wait_flags != nullptr && !B_MN) {
+                    // rows [n0, n0 + BN/2) of the [N, K] weight -> element range of the window -> owning chunks
                     const long long e0 = ag.w_offset + (long long)min(n0, p.N) * p.K;
                     const long long e1 = ag.w_offset + (long long)min(n0 + BN / 2, p.N) * p.K;
                     if (e1 > e0) {
-                        const int c0 = (int)((e0 - ag.layer_start) / ag.chunk), c1 = (int)((e1 - 1 - ag.layer_start) / ag.chunk);
+                        const int c0 = (int)(e0 / ag.chunk), c1 = (int)((e1 - 1) / ag.chunk);
                         for (int c = c0; c <= c1; ++c) {
-                            if (c == ag.rank || (ready_mask >> c) & 1u) continue;
-                            while (__shfl_sync(0xffffffffu, ld_acquire_gpu(ag.flags + c), 0) < ag_epoch) __nanosleep(32);
+                            if ((ready_mask >> c) & 1u) continue;
+                            const long long t0 = clock64();
+                            while (__shfl_sync(0xffffffffu, ld_acquire_gpu(ag.wait_flags + c), 0) < ag_gen) {
+                                __nanosleep(32);
+                                if (clock64() - t0 > 20000000000ll) {      // ~10 s: the gather warps are stuck (dead peer)
+                                    if (lane == 0 && ag.err != nullptr) *ag.err = 1;
+                                    break;
+                                }
+                            }
                             ready_mask |= 1u << c;
                         }
                         asm volatile("fence.proxy.async;" ::: "memory");   // gathered by generic stores, read by TMA
@@ -220,19 +228,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (!OUT_F32 && store_thread) ptx::tma_store_wait_all<0>();
     } else if (AG) {
         // ------------------------------------------------------------------ gather warps (6..9, every CTA)
-        if (ag.gather) {
-            const int gt = (int)threadIdx.x - NUM_THREADS;              // 0..127
-            const int epoch = *ag.epoch;
-            bf16* dst = ag.wb[ag.rank];
-            for (int s = 1; s < ag.world; ++s) {
-                const int src_rank = (ag.rank + s) % ag.world;
-                const long long c_lo = ag.layer_start + (long long)src_rank * ag.chunk;
-                const long long c_hi = c_lo + ag.chunk < ag.layer_end ? c_lo + ag.chunk : ag.layer_end;
-                const bf16* src = ag.wb[src_rank];
+        const int gt = (int)threadIdx.x - NUM_THREADS;              // 0..127
+        const int gen = ag.njobs > 0 ? *ag.gen : 0;
+        for (int j = 0; j < ag.njobs; ++j) {
+            const AgJob& job = ag.job[j];
+            for (int s = 0; s < ag.world; ++s) {
+                const int src_rank = (ag.rank + s) % ag.world;          // own chunk first (local copy), then the peers
+                const long long c_lo = (long long)src_rank * job.chunk;
+                const long long c_hi = c_lo + job.chunk < job.total ? c_lo + job.chunk : job.total;
                 // 16-byte vectors, 4 loads in flight per thread, grid-strided over all CTAs' gather threads
                 const long long nvec = c_hi > c_lo ? (c_hi - c_lo) / 8 : 0;
-                const uint4* sv = reinterpret_cast<const uint4*>(src + c_lo);
-                uint4* dv = reinterpret_cast<uint4*>(dst + c_lo);
+                const uint4* sv = reinterpret_cast<const uint4*>(job.src[src_rank]);
+                uint4* dv = reinterpret_cast<uint4*>(job.dst + c_lo);
                 const long long stride = (long long)gridDim.x * 128;
                 long long i = (long long)blockIdx.x * 128 + gt;
                 for (; i + 3 * stride < nvec; i += 4 * stride) {
@@ -246,11 +253,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 // 2 = these gather warps (the AG variant has ONE epilogue group, so id 2 is free here)
                 asm volatile("bar.sync 2, 128;" ::: "memory");
                 if (gt == 0) {
-                    const unsigned prev = atomicAdd(ag.counters + src_rank, 1u);
+                    const unsigned prev = atomicAdd(job.counters + src_rank, 1u);
                     if (prev == gridDim.x - 1) {
-                        ag.counters[src_rank] = 0;
+                        job.counters[src_rank] = 0;
                         __threadfence();
-                        st_release_gpu(ag.flags_w + src_rank, epoch);
+                        st_release_gpu(job.flags + src_rank, gen);
                     }
                 }
             }
@@ -343,19 +350,26 @@ extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, i
     B200_RETURN_LAUNCH_STATUS("gemm_2cta");
 }
 
-// All-gather fused forward GEMM for sharded data parallelism: C = A * W^T (+bias, ReLU) where W [N, K] is a slot
-// of the flat bf16 weight buffer at element offset w_offset, inside a layer range [layer_start, layer_end) whose
-// `world` chunks are owned by the ranks.  flags/counters: [world] ints (local, zero-initialised once).
-// gather != 0: this launch also pulls every remote chunk of the layer from h_wb[peer] into h_wb[rank]
-// (the first weight-consuming GEMM of the layer); later GEMMs of the layer only wait on the flags.
-extern "C" int b200_gemm_ag(const void* A, void* Cout, int M, int N, int K, long long lda, long long ldc, const float* bias,
-                            int relu, void* relu_bits_out, void* const* h_wb, int world, int rank, long long layer_start,
-                            long long layer_end,
-                            long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev,
-                            int gather, cudaStream_t st) {
+// All-gather fused into a GEMM (sharded data parallelism).  C[M,N] = A[M,K] * opB^T (+bias, ReLU / ReLU sign bits),
+// bf16 out, where B lives in a LOCAL window of gathered layer weights (b_mn = 0: [N,K] forward; 1: [K,N] dgrad).
+// The launch carries up to two gather jobs: four extra warps per CTA copy a layer's chunks from their owners'
+// shards (own chunk first, then the peers over NVLink) into a local window and raise one flag per chunk.
+//   * prefetch: the job belongs to the NEXT layer - its transfer hides under this GEMM's math, and it is complete
+//     when the kernel is, so the consumers need no waiting at all;
+//   * self (wait_flags != null, forward only): the job is this GEMM's own B operand - the tiles whose weight rows
+//     are already in the window run first (n-tile order rotated to the own chunk), the others wait per chunk.
+extern "C" int b200_gemm_ag(const void* A, const void* Bw, void* Cout, int M, int N, int K, long long lda, long long ldb,
+                            long long ldc, int b_mn, const float* bias, int relu, void* relu_bits_out, const void* relu_bits,
+                            const int* wait_flags, long long wait_chunk, long long w_offset, int world, int rank,
+                            const int* gen_dev, int* err, int njobs,
+                            void* const* h_src0, void* dst0, long long chunk0, long long total0, int* flags0, void* counters0,
+                            void* const* h_src1, void* dst1, long long chunk1, long long total1, int* flags1, void* counters1,
+                            cudaStream_t st) {
     B200_REQUIRE(world >= 1 && world <= 8, "gemm_ag: world size %d not supported", world);
-    B200_REQUIRE(M > 0 && N > 0 && K > 0 && lda % 8 == 0 && ldc % 8 == 0 && K % 8 == 0, "gemm_ag: bad shape / alignment");
-    B200_REQUIRE(layer_start % 8 == 0 && chunk % 8 == 0 && w_offset % 8 == 0, "gemm_ag: offsets must be multiples of 8");
+    B200_REQUIRE(M > 0 && N > 0 && K > 0 && lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "gemm_ag: bad shape / alignment");
+    B200_REQUIRE(njobs >= 0 && njobs <= 2, "gemm_ag: at most two gather jobs per launch");
+    B200_REQUIRE(wait_flags == nullptr || (!b_mn && wait_chunk > 0 && wait_chunk % 8 == 0 && w_offset % 8 == 0),
+                 "gemm_ag: in-kernel waiting needs a K-major B operand and 16-byte aligned chunks");
     constexpr int BN = 256;
     Params p;
     memset(&p, 0, sizeof(p));
@@ -365,23 +379,37 @@ extern "C" int b200_gemm_ag(const void* A, void* Cout, int M, int N, int K, long
     p.num_kb = (K + BK - 1) / BK;
     p.splits = 1; p.kb_per_split = p.num_kb;
     p.alpha = 1.f; p.bias = bias; p.relu = relu; p.relu_bits_out = (unsigned long long*)relu_bits_out;
-    // start with the n-tiles whose weight rows this rank owns
-    const long long own = layer_start + (long long)rank * chunk - w_offset;
-    if (own > 0 && own < (long long)N * K) p.n_shift = (int)(((own + K - 1) / K + BN - 1) / BN) % p.num_n;
+    p.relu_bits = (const unsigned long long*)relu_bits;
     AgParams ag;
     memset(&ag, 0, sizeof(ag));
-    ag.flags = flags; ag.flags_w = flags; ag.epoch = epoch_dev; ag.layer_start = layer_start; ag.layer_end = layer_end;
-    ag.chunk = chunk; ag.w_offset = w_offset; ag.world = world; ag.rank = rank; ag.gather = gather;
-    ag.counters = (unsigned int*)counters;
-    for (int r = 0; r < world; ++r) ag.wb[r] = (bf16*)h_wb[r];
-    const bf16* W = (const bf16*)h_wb[rank] + w_offset;
+    ag.wait_flags = wait_flags; ag.gen = gen_dev; ag.chunk = wait_chunk; ag.w_offset = w_offset;
+    ag.world = world; ag.rank = rank; ag.njobs = njobs; ag.err = err;
+    if (wait_flags != nullptr) {
+        // start with the n-tiles whose weight rows this rank owns (they are copied first, from local memory)
+        const long long own = (long long)rank * wait_chunk - w_offset;
+        if (own > 0 && own < (long long)N * K) p.n_shift = (int)(((own + K - 1) / K + BN - 1) / BN) % p.num_n;
+    }
+    void* const* srcs[2] = {h_src0, h_src1};
+    void* dsts[2] = {dst0, dst1};
+    const long long chunks[2] = {chunk0, chunk1}, totals[2] = {total0, total1};
+    int* flags[2] = {flags0, flags1};
+    void* counters[2] = {counters0, counters1};
+    for (int j = 0; j < njobs; ++j) {
+        B200_REQUIRE(srcs[j] && dsts[j] && flags[j] && counters[j] && chunks[j] % 8 == 0 && totals[j] % 8 == 0,
+                     "gemm_ag: incomplete or misaligned gather job %d", j);
+        for (int r = 0; r < world; ++r) ag.job[j].src[r] = (const bf16*)srcs[j][r];
+        ag.job[j].dst = (bf16*)dsts[j]; ag.job[j].chunk = chunks[j]; ag.job[j].total = totals[j];
+        ag.job[j].flags = flags[j]; ag.job[j].counters = (unsigned int*)counters[j];
+    }
     CUtensorMap tA, tB, tC;
     if (tma::make_2d(&tA, A, M, K, lda * 2, 64, 128, 2)) return -1;
-    if (tma::make_2d(&tB, W, N, K, (uint64_t)K * 2, 64, BN / 2, 2)) return -1;
+    if (!b_mn) { if (tma::make_2d(&tB, Bw, N, K, ldb * 2, 64, BN / 2, 2)) return -1; }
+    else       { if (tma::make_2d(&tB, Bw, K, N, ldb * 2, 64, 64, 2)) return -1; }
     if (tma::make_2d(&tC, Cout, M, N, ldc * 2, 64, 128, 2)) return -1;
     const int sms = b200_num_sms();
     const int nunits = p.num_m * p.num_n;
     const int grid = 2 * min(nunits, sms / 2);
-    if (launch2<BN, false, false, false, true>(tA, tB, tC, p, grid, st, &ag)) return -1;
+    if (!b_mn) { if (launch2<BN, false, false, false, true>(tA, tB, tC, p, grid, st, &ag)) return -1; }
+    else       { if (launch2<BN, false, true, false, true>(tA, tB, tC, p, grid, st, &ag)) return -1; }
     B200_RETURN_LAUNCH_STATUS("gemm_ag");
 }

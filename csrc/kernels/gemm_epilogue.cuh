@@ -41,18 +41,26 @@ struct Params {
 // All-gather fused into the GEMM (sharded data parallelism): the B operand (a weight matrix) lives in a flat
 // bf16 buffer whose layer range [layer_start, layer_end) is split in `world` contiguous chunks, chunk c owned
 // (kept up to date) by rank c.  flags[c] >= *epoch means chunk c of this layer is valid in the LOCAL buffer.
-struct AgParams {
-    const int* flags;         // [world] local "chunk gathered" flags of this layer (null: feature off)
-    const int* epoch;         // device step counter
-    long long layer_start;    // element offsets in the flat bf16 weight buffer
-    long long layer_end;
+// All-gather jobs a GEMM launch can carry (sharded data parallelism, csrc/comm/zero.cu + gemm2.cu).  A job copies one
+// layer's bf16 weights, chunk by chunk, from the ranks that own them (peer-mapped shard memory, generic loads over
+// NVLink) into a local window; the GEMM's own B operand is always a TMA tensor map over LOCAL memory (the window).
+struct AgJob {
+    const bf16* src[8];       // src[r]: rank r's chunk of the layer (own rank: the local shard)
+    bf16* dst;                // local window that receives the whole layer
     long long chunk;          // elements per rank
-    long long w_offset;       // first element of this GEMM's weight matrix
-    int world, rank;
-    int gather;               // 1: this launch also PULLS the layer's remote chunks (first consumer GEMM of the layer)
-    bf16* wb[8];              // peer-mapped flat bf16 weight buffers (index = rank; own buffer included)
-    int* flags_w;             // same flags, writable
+    long long total;          // elements of the layer (the last chunk may be short)
+    int* flags;               // [world] raised to *gen once chunk c sits in the window
     unsigned int* counters;   // [world] zero-initialised arrival counters
+};
+struct AgParams {
+    const int* wait_flags;    // flags of the window that holds THIS GEMM's B operand (null: B is complete, no waiting)
+    const int* gen;           // device-side gather generation (incremented once per forward / backward pass)
+    long long chunk;          // elements per rank of the B operand's layer
+    long long w_offset;       // first element of the B operand inside its window
+    int world, rank;
+    int njobs;                // gather jobs carried by this launch (0..2); the first may be the B operand's own layer
+    int* err;                 // raised when a wait times out
+    AgJob job[2];
 };
 
 // tfull_bar: local mbarrier (shared::cta address) the MMA issuer commits to; taddr: TMEM address of this

@@ -82,13 +82,14 @@ int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long l
  * stages half of the operands, 6-8 pipeline stages.  The default for large problems. */
 int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out, const void* relu_bits, int bn, int split_k, cudaStream_t st);
 
-/* All-gather fused into the forward GEMM (sharded data parallelism, ref: absent in the reference - SURVEY N6/T11):
- * C[M,N] = A[M,K] * W^T (+bias) (ReLU), W [N,K] = a slot of the flat bf16 weight buffer at element w_offset inside
- * a layer range [layer_start, layer_end) whose `world` equal chunks are owned by the ranks.  h_wb: host array of the
- * peer-mapped flat weight buffers.  flags / counters: [world] ints on this device, zero-initialised once.
- * gather != 0: this launch's extra warps pull every remote chunk of the layer over NVLink into the local buffer and
- * raise flags[c] = *epoch_dev; tiles whose rows are already local run meanwhile, the others wait per chunk. */
-int b200_gemm_ag(const void* A, void* C, int M, int N, int K, long long lda, long long ldc, const float* bias, int relu, void* relu_bits_out, void* const* h_wb, int world, int rank, long long layer_start, long long layer_end, long long chunk, long long w_offset, int* flags, void* counters, const int* epoch_dev, int gather, cudaStream_t st);
+/* All-gather fused into a GEMM (sharded data parallelism; absent in the reference - SURVEY N6/T11).
+ * C[M,N] = A[M,K] * opB^T (+bias) (ReLU -> relu_bits_out | masked by relu_bits), bf16 out; Bw points into a LOCAL
+ * window of gathered layer weights (b_mn = 0: [N,K]; 1: [K,N]).  The launch carries njobs (0..2) gather jobs: extra
+ * warps copy a layer chunk by chunk from h_srcJ[r] (rank r's chunk in its peer-mapped bf16 shard; own chunk first)
+ * into dstJ + r * chunkJ (totalJ elements in all) and raise flagsJ[r] = *gen_dev; countersJ: [world] zeroed ints.
+ * wait_flags != null (K-major B only): the B operand's own window is being filled by job 0 of this very launch -
+ * tiles wait per chunk (wait_chunk elements per rank, B starts at element w_offset of the window), own rows first. */
+int b200_gemm_ag(const void* A, const void* Bw, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int b_mn, const float* bias, int relu, void* relu_bits_out, const void* relu_bits, const int* wait_flags, long long wait_chunk, long long w_offset, int world, int rank, const int* gen_dev, int* err, int njobs, void* const* h_src0, void* dst0, long long chunk0, long long total0, int* flags0, void* counters0, void* const* h_src1, void* dst1, long long chunk1, long long total1, int* flags1, void* counters1, cudaStream_t st);
 
 /* Weight-streaming GEMM for decode-sized batches (M <= 128): out[M,N] = act(x[M,K] @ W[N,K]^T + bias), operands
  * swapped so the weight tile is the 128-row MMA operand; K is split over the CTAs of a thread-block cluster
@@ -177,9 +178,22 @@ int b200_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, lo
  * sig: int[2][world][num_buckets] per rank (ready | done), zero-initialised; *epoch_dev: 1, 2, 3, ...
  * (a device int the caller increments once per step, so a captured graph can be replayed);
  * m, v: this rank's moments for the slice; h_slot_end / h_slot_fp32: element end offsets and
- * "consumers read fp32" flags of the parameter slots inside the bucket.  zero_mode != 0: bf16-only slots
- * (weight matrices) are NOT pushed to the peers - they stay sharded and are pulled by b200_gemm_ag. */
-int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start, long long n, float* m, float* v, const float* hyper, const long long* h_slot_end, const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas, int zero_mode, cudaStream_t st);
+ * "consumers read fp32" flags of the parameter slots inside the bucket.
+ * mc_grad / mc_wb / mc_flat (all three or none): multicast mappings of the same buffers; when given, the pull is a
+ * multimem.ld_reduce (summed inside the NVSwitch) and each push one multimem.st replicated by the switch. */
+int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_flat, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long start, long long n, float* m, float* v, const float* hyper, const long long* h_slot_end, const int* h_slot_fp32, int n_slots, void* cta_counter, int* err, int ctas, void* mc_grad, void* mc_wb, void* mc_flat, cudaStream_t st);
+/* Sharded mode (csrc/comm/zero.cu): same fused reduce + AdamW, but nothing full-size is kept - h_grad[r] is rank r's
+ * gradient buffer OF THIS BUCKET (a rolling window or the head / embedding buffer; mc_grad its multicast mapping or
+ * null), the owned slice [lo, lo+n) of the bucket is reduced (multimem.ld_reduce or W peer loads), master / m / v /
+ * shard16 are this rank's slices (fp32 master, moments, bf16 shard the peers' all-gather reads), and parameters
+ * consumed in fp32 are also stored into every rank's small replicated store (h_small / mc_small) at
+ * bucket offset + h_slot_small_off[k] (slots whose value is -(1<<62) are not small). */
+int b200_zero_reduce_adamw(void* const* h_grad, void* mc_grad, void* const* h_small, void* mc_small, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long lo, long long n, float* master, float* m, float* v, void* shard16, const float* hyper, const long long* h_slot_end, const long long* h_slot_small_off, int n_slots, void* cta_counter, int* err, int ctas, cudaStream_t st);
+/* blocks the stream until every rank's done flag of buckets [bucket_lo, bucket_hi) has reached *epoch_dev - lag */
+int b200_zero_wait(const int* sig, int world, int num_buckets, int bucket_lo, int bucket_hi, const int* epoch_dev, int lag, int* err, cudaStream_t st);
+/* x[b*T+t, :] = wte[idx[b,t], :] + wpe[t, :] with the fp32 tables sharded: h_shard[r] = rank r's master slice of the
+ * embedding bucket (chunk elements per rank), wte_off / wpe_off = element offsets of the two tables in the bucket */
+int b200_embed_fwd_sharded(const long long* idx, void* const* h_shard, int world, long long chunk, long long wte_off, long long wpe_off, float* x, int B, int T, int d, int V, cudaStream_t st);
 /* blocks the stream until every owner's done flag of every bucket has reached `epoch` */
 int b200_dp_wait_done(const int* sig, int world, int num_buckets, const int* epoch_dev, int* err, cudaStream_t st);
 

@@ -77,6 +77,8 @@ class Transformer(nn.Module):
 
     # ------------------------------------------------------------------ engine dispatch
     def _native_ok(self) -> bool:
+        if self.use_native and self._engine is not None and getattr(self._engine, "store", None) is not None:
+            return True          # sharded data parallelism: the parameters live in the engine's shards, not in _flat
         if not self.use_native or self._flat is None or self._flat.device.type != "cuda":
             return False
         if self._flat.dtype != torch.float32:
@@ -161,6 +163,9 @@ class Transformer(nn.Module):
         if args:  # legacy positional (destination, prefix, keep_vars)
             destination = args[0]
             prefix = args[1] if len(args) > 1 else prefix
+        if self._flat is None:
+            raise RuntimeError("the parameters are sharded across ranks (dp_mode='zero'): call "
+                               "engine.dp.gather_full_state() on every rank first (Trainer.save_checkpoint does)")
         sd = self.layout.to_reference_state_dict(self._flat, clone=not keep_vars)
         out = destination if destination is not None else OrderedDict()
         for k, v in sd.items():
@@ -172,6 +177,9 @@ class Transformer(nn.Module):
                            for n in self.layout.slots)
 
     def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        if self._flat is None:
+            raise RuntimeError("the parameters are sharded across ranks (dp_mode='zero'): call "
+                               "engine.dp.materialize() on every rank first (Trainer.load_checkpoint does)")
         missing, unexpected = self.layout.from_reference_state_dict(self._flat, state_dict, strict)
         if self._engine is not None:
             self._engine.params_changed()

@@ -74,8 +74,9 @@ def plan_buckets(layout: ParamLayout, world: int, vocab_parallel: bool = False) 
 class DataParallel:
     def __init__(self, eng, ctx, mode: str = "ddp", ctas: int = 0, ctas_tail: int = 0, vocab_parallel: bool = False):
         from .symm import SymmBuffer
-        if mode not in ("ddp", "zero"):
-            raise ValueError(mode)
+        if mode != "ddp":
+            raise ValueError(f"DataParallel is the replicated mode; dp_mode={mode!r} is parallel.zero.ZeroDataParallel "
+                             "(use parallel.make_data_parallel)")
         import os
         # CTAs per reduce kernel.  Measured at W=2 (bench.py, ms/step): 8 -> 23.2, 16 -> 22.0, 32 -> 21.1, 148 -> 20.4:
         # the kernel is bandwidth/latency bound and co-resides with the GEMM CTAs without slowing them much
@@ -95,7 +96,12 @@ class DataParallel:
         self.sym_grad = SymmBuffer(n * 4, self.rank, self.world, dev)
         self.sym_wb = SymmBuffer(n * 2, self.rank, self.world, dev)
         self.sym_flat = SymmBuffer(n * 4, self.rank, self.world, dev)
-        self.sym_sig = SymmBuffer(2 * self.world * self.nb * 4, self.rank, self.world, dev)
+        self.sym_sig = SymmBuffer(2 * self.world * self.nb * 4, self.rank, self.world, dev, multicast=False)
+        # NVSwitch multicast mappings of the three buffers (all or none): the reduce kernel then pulls with
+        # multimem.ld_reduce and pushes with multimem.st
+        mcs = (self.sym_grad.mc_ptr, self.sym_wb.mc_ptr, self.sym_flat.mc_ptr)
+        self.multicast = all(mcs) and os.environ.get("B200_DP_MULTIMEM", "1") == "1"
+        self.mc_ptrs = tuple(ctypes.c_void_p(p) for p in mcs) if self.multicast else (None, None, None)
         new_flat = self.sym_flat.view(F32)[:n]
         new_flat.copy_(eng.flat)
         dist.broadcast(new_flat, src=0)                   # identical replicas to start from
@@ -119,12 +125,7 @@ class DataParallel:
         for _, cnt in self.owned:
             self.opt_off.append(off)
             off += cnt
-        # sharded-weight ("zero") mode: per-layer, per-source-rank "chunk gathered" flags + arrival counters, and the
-        # weight version they are compared against (bumped after every optimizer step)
-        self.zero = mode == "zero"
-        self.ag_flags = torch.zeros(max(lay.L, 1), self.world, device=dev, dtype=torch.int32)
-        self.ag_counters = torch.zeros(max(lay.L, 1), self.world, device=dev, dtype=torch.int32)
-        self.version_dev = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.zero = False
         self.counter = torch.zeros(self.nb, device=dev, dtype=torch.int32)
         self.err = torch.zeros(1, device=dev, dtype=torch.int32)
         self.epoch_dev = torch.zeros(1, device=dev, dtype=torch.int32)   # incremented on the device each step
@@ -163,8 +164,7 @@ class DataParallel:
                                     self.m[off:].data_ptr(), self.v[off:].data_ptr(), self.eng.hyper.data_ptr(),
                                     end_arr, fp_arr, k, self.counter[b:].data_ptr(), self.err.data_ptr(),
                                     self.ctas_tail if tail else self.ctas,
-                                    1 if (self.zero and self.plans[b].name.startswith("block")) else 0,
-                                    self.comm_stream.cuda_stream)
+                                    *self.mc_ptrs, self.comm_stream.cuda_stream)
         lib.check(rc, "dp_reduce_adamw")
         ops.LAUNCHES += 1
         self._launched.add(b)
@@ -186,51 +186,13 @@ class DataParallel:
                                           self.epoch_dev.data_ptr(), self.err.data_ptr(), main.cuda_stream)
         lib.check(rc, "dp_wait_done")
         ops.LAUNCHES += 1
-        if self.zero:
-            ops.incr_int(self.version_dev, 1)            # the sharded matrices changed: next forward re-gathers
         self._launched = set()
 
-    # ------------------------------------------------------------------ sharded weights ("zero" mode)
-    def gemm_ag(self, layer: int, slot_name: str, a: torch.Tensor, out: torch.Tensor, bias=None, relu: bool = False,
-                gather: bool = False, relu_bits_out=None) -> None:
-        """Forward GEMM of a block whose weight matrix is sharded across the ranks: the all-gather of the layer's
-        weights is fused into the (first) GEMM that consumes them (csrc/kernels/gemm2.cu, b200_gemm_ag)."""
-        lay = self.eng.layout
-        plan = self.plans[self.index[f"block{layer}"]]
-        slot = lay.slots[slot_name]
-        N, K = slot.shape
-        M = a.shape[0]
-        rc = lib.load().b200_gemm_ag(a.data_ptr(), out.data_ptr(), M, N, K, a.stride(0), out.stride(0),
-                                     None if bias is None else bias.data_ptr(), int(relu),
-                                     None if relu_bits_out is None else relu_bits_out.data_ptr(), self.sym_wb.ptr_array,
-                                     self.world, self.rank, plan.start, plan.end, plan.chunk, slot.offset,
-                                     self.ag_flags[layer].data_ptr(), self.ag_counters[layer].data_ptr(),
-                                     self.version_dev.data_ptr(), int(gather), torch.cuda.current_stream().cuda_stream)
-        lib.check(rc, "gemm_ag")
-        ops.LAUNCHES += 1
-
     def gather_weights(self) -> None:
-        """Bring every remote chunk of every block into the local bf16 shadow with plain peer copies (used off the
-        hot path: before generation / evaluation with small shapes, where the GEMMs are not the AG kind)."""
+        """Make the local bf16 weights complete (vocab-parallel LM head: all-gather its slices); replicated weights
+        already are."""
         if self.vp is not None:
             self.vp.gather_full(with_moments=False)
-        if not self.zero:
-            return
-        from .symm import _CudaArray
-        n = self.eng.layout.total
-        torch.cuda.synchronize()
-        dist.barrier()
-        for r in range(self.world):
-            if r == self.rank:
-                continue
-            peer = torch.as_tensor(_CudaArray(self.sym_wb.ptrs[r], n * 2), device=self.eng.device).view(BF16)
-            for p in self.plans:
-                if p.name.startswith("block"):
-                    s, c = p.slice_of(r)
-                    self.eng.wb[s:s + c].copy_(peer[s:s + c])
-        self.ag_flags.fill_(int(self.version_dev.item()))
-        torch.cuda.synchronize()
-        dist.barrier()
 
     def begin_step(self) -> None:
         """First thing of a step (main stream): advance the device-side epoch."""

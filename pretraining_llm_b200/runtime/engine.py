@@ -102,32 +102,35 @@ class Engine:
         self.hyper = torch.zeros(8, device=self.device, dtype=F32)
         self.betas, self.eps, self.weight_decay = (0.9, 0.999), 1e-8, 0.01   # torch.optim.AdamW defaults
         self.ws: Dict[Tuple[int, int, bool], Workspace] = {}
-        self.dp = None                     # parallel.dp.DataParallel, set by attach_dp()
+        self.dp = None                     # parallel.dp.DataParallel / parallel.zero.ZeroDataParallel
+        self.store = None                  # sharded mode: the object that serves P / W / G instead of the flat buffers
         self.launches_per_step = 0
         self._gen = None
 
     # ------------------------------------------------------------------ parameters
-    def W(self, name: str) -> torch.Tensor:       # bf16 shadow view
-        return self.layout.view(self.wb, name)
+    def W(self, name: str) -> torch.Tensor:       # bf16 weights the GEMMs read (flat shadow, or a gathered window)
+        return self.store.W(name) if self.store is not None else self.layout.view(self.wb, name)
 
-    def P(self, name: str) -> torch.Tensor:       # fp32 master view
-        return self.layout.view(self.flat, name)
+    def P(self, name: str) -> torch.Tensor:       # fp32 parameters consumed in fp32 (LayerNorm, biases, embeddings)
+        return self.store.P(name) if self.store is not None else self.layout.view(self.flat, name)
 
-    def G(self, name: str) -> torch.Tensor:       # fp32 gradient view
-        return self.layout.view(self.grad, name)
+    def G(self, name: str) -> torch.Tensor:       # fp32 gradient view (flat buffer, or a rolling window)
+        return self.store.G(name) if self.store is not None else self.layout.view(self.grad, name)
 
     def params_changed(self) -> None:
         self._wb_version = -1
 
     def sync_weights(self) -> None:
         """Refresh the bf16 shadow if the fp32 masters were modified by anyone but our AdamW."""
+        if self.store is not None:
+            return                         # sharded: the reduce kernel keeps the bf16 shards in step with the masters
         v = self.flat._version
         if v != self._wb_version:
             ops.cast_bf16(self.flat, self.wb)
             self._wb_version = v
 
     def ensure_grad(self) -> None:
-        if self.grad is None:
+        if self.grad is None and self.store is None:
             self.grad = torch.zeros_like(self.flat)
 
     def ensure_opt_state(self) -> None:
@@ -155,6 +158,9 @@ class Engine:
     def _blocks_forward(self, w: Workspace, kv=None, pos0: int = 0) -> None:
         lay = self.layout
         B, T, L, H, hs = w.B, w.T, lay.L, lay.H, lay.hs
+        z = self.store
+        if z is not None:
+            z.begin_pass()                 # sharded weights: a new all-gather generation
         for l in range(L):
             s = l if w.train else 0
             pre = f"attn_blocks.{l}."
@@ -167,9 +173,8 @@ class Engine:
                 sp = (l - 1) if w.train else 0
                 ops.ln_fwd(w.resid_b[sp], self.P(pre + "ln1.weight"), self.P(pre + "ln1.bias"), branch=w.mlp_out,
                            x_out=ra_in, out=w.h1[s], mean=st1[0], rstd=st1[1])
-            zero = self.dp is not None and self.dp.zero and w.M >= 512
-            if zero:   # sharded weights: all-gather of the layer fused into its first GEMM
-                self.dp.gemm_ag(l, pre + "attn.wqkv", w.h1[s], w.qkv[s], gather=True)
+            if z is not None:  # sharded weights: this GEMM also carries the all-gather of the next layer
+                z.gemm_fwd(l, w.h1[s], w.qkv[s])
             else:
                 ops.gemm(w.h1[s], self.W(pre + "attn.wqkv"), out=w.qkv[s])
             if kv is not None:
@@ -177,14 +182,9 @@ class Engine:
             ops.attn_fwd(w.qkv[s], B, T, H, hs, out=w.att[s], lse=w.lse[s])
             ops.ln_fwd(ra_in, self.P(pre + "ln2.weight"), self.P(pre + "ln2.bias"), branch=w.att[s],
                        x_out=w.resid_b[s], out=w.h2[s], mean=st2[0], rstd=st2[1])
-            if zero:
-                self.dp.gemm_ag(l, pre + "mlp.hidden.weight", w.h2[s], w.act[s], bias=self.P(pre + "mlp.hidden.bias"),
-                                relu=True, relu_bits_out=w.relu_bits[s] if w.train else None)
-                self.dp.gemm_ag(l, pre + "mlp.proj.weight", w.act[s], w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
-            else:
-                ops.gemm(w.h2[s], self.W(pre + "mlp.hidden.weight"), out=w.act[s],
-                         bias=self.P(pre + "mlp.hidden.bias"), relu=True, relu_bits_out=w.relu_bits[s] if w.train else None)
-                ops.gemm(w.act[s], self.W(pre + "mlp.proj.weight"), out=w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
+            ops.gemm(w.h2[s], self.W(pre + "mlp.hidden.weight"), out=w.act[s],
+                     bias=self.P(pre + "mlp.hidden.bias"), relu=True, relu_bits_out=w.relu_bits[s] if w.train else None)
+            ops.gemm(w.act[s], self.W(pre + "mlp.proj.weight"), out=w.mlp_out, bias=self.P(pre + "mlp.proj.bias"))
         sl = (L - 1) if w.train else 0
         sf = L if w.train else 1
         stf = w.ln_stats[2 * (L if w.train else 1)]
@@ -211,7 +211,10 @@ class Engine:
 
     def _forward_ws(self, w: Workspace, with_loss: bool, loss_scale: float = 1.0) -> None:
         lay = self.layout
-        ops.embed_fwd(w.idx, self.P("token_embed.weight"), self.P("position_embed.weight"), out=w.resid_a[0])
+        if self.store is not None:         # sharded fp32 tables: rows come from their owners over NVLink
+            self.store.embed_fwd(w.idx, w.resid_a[0])
+        else:
+            ops.embed_fwd(w.idx, self.P("token_embed.weight"), self.P("position_embed.weight"), out=w.resid_a[0])
         self._blocks_forward(w)
         V = lay.V
         if with_loss and w.train and self.dp is not None and self.dp.vp is not None:
@@ -237,6 +240,12 @@ class Engine:
         lay = self.layout
         B, T, M, L, H, hs, V = w.B, w.T, w.M, lay.L, lay.H, lay.hs, lay.V
         fm = 1 if accumulate else 0
+        z = self.store
+        if z is not None:
+            if accumulate or not dp_sync:
+                raise NotImplementedError("sharded mode reduces every layer's gradients as soon as they exist: "
+                                          "gradient accumulation needs dp_mode='ddp'")
+            z.begin_pass()
         if not accumulate:
             self.G("token_embed.weight").zero_()     # scatter-add target
         # LM head + CE
@@ -255,12 +264,17 @@ class Engine:
         for l in reversed(range(L)):
             pre = f"attn_blocks.{l}."
             st1, st2 = w.ln_stats[2 * l], w.ln_stats[2 * l + 1]
+            if z is not None:
+                z.before_layer_bwd(l)          # the gradient window of layer l+2 must have been reduced by every rank
             # ---- MLP
             ops.gemm(w.dx_bf16, w.act[l], out=self.G(pre + "mlp.proj.weight"), a_mn=True, b_mn=True, f32_mode=fm)
             ops.gemm(w.dx_bf16, self.W(pre + "mlp.proj.weight"), out=w.dh, b_mn=True, relu_bits=w.relu_bits[l])
             ops.colsum(w.dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
             ops.gemm(w.dh, w.h2[l], out=self.G(pre + "mlp.hidden.weight"), a_mn=True, b_mn=True, f32_mode=fm)
-            ops.gemm(w.dh, self.W(pre + "mlp.hidden.weight"), out=w.dtmp, b_mn=True)
+            if z is not None:                  # carries the all-gather of layer l-1's weights for its backward
+                z.gemm_bwd(l, w.dh, w.dtmp)
+            else:
+                ops.gemm(w.dh, self.W(pre + "mlp.hidden.weight"), out=w.dtmp, b_mn=True)
             # LayerNorm backward in two steps: the partial sums of ln2 and ln1 are reduced by ONE launch at the end of the block
             ops.ln_bwd_partial(w.dtmp, w.resid_b[l], st2[0], st2[1], self.P(pre + "ln2.weight"), w.ln_partial,
                                dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16, with_colsum=True)
@@ -306,10 +320,11 @@ class Engine:
             self.ensure_opt_state()
             ops.adamw(self.flat, self.grad, self.exp_avg, self.exp_avg_sq, self.wb, self.hyper)
         # our kernel wrote the masters and the shadow together: keep them marked in sync
-        self._wb_version = self.flat._version
+        if self.flat is not None:
+            self._wb_version = self.flat._version
 
     def zero_grad(self) -> None:
-        if self.grad is not None:
+        if self.grad is not None and self.store is None:
             self.grad.zero_()
 
     # ------------------------------------------------------------------ whole training step
@@ -353,6 +368,9 @@ class Engine:
     # ------------------------------------------------------------------ nn.Module facade path
     def module_forward(self, idx: torch.Tensor, targets: Optional[torch.Tensor]):
         grad_mode = torch.is_grad_enabled() and targets is not None and self.model.training
+        if grad_mode and self.store is not None:
+            raise RuntimeError("the autograd (torch-optimizer) path needs full parameters; with dp_mode='zero' use "
+                               "Engine.train_step / Trainer")
         idx = idx.contiguous()
         if idx.dtype != torch.int64:
             idx = idx.long()
@@ -370,7 +388,8 @@ class Engine:
     def generate(self, idx, max_new_tokens, **kw):
         from .generation import Generator
         if self.dp is not None:
-            self.dp.gather_weights()          # sharded mode: small-shape GEMMs read the local shadow
+            # vocab-parallel / sharded weights -> a complete local copy for the small-shape decode kernels
+            getattr(self.dp, "prepare_generation", self.dp.gather_weights)()
         if self._gen is None:
             self._gen = Generator(self)
         return self._gen.generate(idx, max_new_tokens, **kw)

@@ -60,9 +60,9 @@ class Trainer:
         self.tokens_per_step = None
         self.log_file = open(self.config["log_jsonl"], "a") if self.config.get("log_jsonl") and self.dist.master else None
         if self.native and self.dist.world > 1:
-            from ..parallel.dp import DataParallel
-            model.engine.dp = DataParallel(model.engine, self.dist, mode=self.config.get("dp_mode", "ddp"),
-                                           vocab_parallel=bool(self.config.get("vocab_parallel", False)))
+            from ..parallel import make_data_parallel
+            make_data_parallel(model.engine, self.dist, self.config.get("dp_mode", "ddp"),
+                               bool(self.config.get("vocab_parallel", False)))
 
     # reference-compatible private names
     def _get_lr(self, it: int) -> float:
@@ -153,6 +153,9 @@ class Trainer:
                                                             eng.betas, eng.eps, eng.weight_decay)
             if eng.dp is not None:
                 eng.release_full_opt_state()      # the sharded dp.m / dp.v are the live copies
+                if hasattr(eng.dp, "release_full"):
+                    sd = {k: v.cpu() for k, v in sd.items()}
+                    eng.dp.release_full()         # sharded mode: drop the materialised full parameters again
         else:
             osd = self._reference_optimizer_state()
         return {"model_state_dict": sd, "optimizer_state_dict": osd,
@@ -184,6 +187,9 @@ class Trainer:
 
     def load_checkpoint(self, path: str) -> None:
         ckpt = torch.load(path, map_location="cpu", weights_only=False)
+        sharded = self.native and self.model.engine.dp is not None and hasattr(self.model.engine.dp, "materialize")
+        if sharded:
+            self.model.engine.dp.materialize()     # collective: full buffers to load into, re-sharded below
         self.model.load_state_dict(ckpt["model_state_dict"])
         osd = ckpt.get("optimizer_state_dict")
         lay = self.model.layout
@@ -205,6 +211,8 @@ class Trainer:
                     self.optimizer.state[p] = {"step": torch.tensor(float(step)),
                                                "exp_avg": lay.view(m, name).clone().to(p.device),
                                                "exp_avg_sq": lay.view(v, name).clone().to(p.device)}
+        if sharded and self.model.engine.dp.full_flat is not None:
+            self.model.engine.dp.state_loaded()    # no optimizer state in the file: re-shard the weights alone
         ts = ckpt.get("trainer_state")
         if ts:
             self.step = int(ts["step"])
