@@ -136,7 +136,12 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
         }
         const uint2 pb = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
         *reinterpret_cast<float4*>(p_master + e) = pv;
-        if (MC) {
+        if (need32 == 2) {
+            // embedding tables: nobody consumes a bf16 copy, and embed_fwd reads the fp32 rows from their OWNER over
+            // NVLink (b200_embed_fwd_sharded) - nothing to push.  This is the bucket backward finishes last, so its
+            // reduce is the exposed one: no 206 MB of outgoing stores behind the last backward kernel.
+            *reinterpret_cast<uint2*>(P.wb[rank] + e) = pb;
+        } else if (MC) {
             multimem_st_bf16x4(P.mc_wb + e, pb);
             if (need32) multimem_st_f4(P.mc_flat + e, pv);
         } else {

@@ -9,6 +9,12 @@
 // along K): each leaves its fp32 partial tile in its own shared memory, and after a cluster barrier every CTA
 // reduces a slice of the batch rows by reading its peers' tiles through distributed shared memory - no global
 // scratch, no atomics, no second kernel.
+//
+// Programmatic dependent launch: the kernel is launched with programmatic stream serialisation, lets ITS dependents
+// go at once, and its TMA producer fills the whole smem ring with WEIGHT tiles before griddepcontrol.wait - weights do
+// not depend on the previous kernel, so up to STAGES x 16 KiB x 148 CTAs (24 MB, most of a layer matrix) are already in
+// flight while the LayerNorm / attention kernel that produces the activations is still running.  Only the activation
+// loads (and everything downstream of them through the mbarrier chain) come after the wait.
 // Replaces the per-token full-context fp32 forward of the reference's generate (src/models/transformer.py:107-113).
 #include <cuda.h>
 
@@ -52,6 +58,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 1);
     uint8_t* smem_gen = smem_raw + (smem_base - ptx::smem_u32(smem_raw));
 
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
     const int n_tile = blockIdx.x, split = blockIdx.y;
     const int n0 = n_tile * 128;
@@ -74,15 +81,25 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
-    pdl_sync();   // prologue done: from here on we touch memory owned by earlier kernels
     const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base)), 0);
 
     if (warp == 0) {
         // whole warp converged; one elected lane executes each wrapper (uniform operands, see ptx.cuh)
         {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int kb = kb0; kb < kb1; ++kb) {
+            // 1. weights of the first ring pass: independent of every earlier kernel, issued before the grid dependency
+            const int npre = min(kb1 - kb0, C::STAGES);
+            for (int i = 0; i < npre; ++i) {
+                ptx::mbar_arrive_expect_tx_w(full_bar(i), C::STAGE_BYTES);
+                ptx::tma_load_2d_w(smem_base + i * C::STAGE_BYTES, &tmW, full_bar(i), (kb0 + i) * BK, n0);
+            }
+            // 2. the activations are the previous kernel's output: wait for it (and, transitively, all earlier kernels)
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            for (int i = 0; i < npre; ++i)
+                ptx::tma_load_2d_w(smem_base + i * C::STAGE_BYTES + A_BYTES, &tmX, full_bar(i), (kb0 + i) * BK, 0);
+            // 3. steady state
+            int stage = npre == C::STAGES ? 0 : npre;
+            uint32_t phase = npre == C::STAGES ? 1 : 0;
+            for (int kb = kb0 + npre; kb < kb1; ++kb) {
                 ptx::mbar_wait(empty_bar(stage), phase ^ 1);
                 ptx::mbar_arrive_expect_tx_w(full_bar(stage), C::STAGE_BYTES);
                 const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
@@ -205,9 +222,13 @@ int launch_skinny(const CUtensorMap& tW, const CUtensorMap& tX, const SParams& p
     attr[0].val.clusterDim.z = 1;
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
-    const char* e = getenv("B200_PDL");
+    static int pdl = -1;
+    if (pdl < 0) {
+        const char* e = getenv("B200_PDL_SKINNY");                // on by default for THIS kernel (weight prefetch under
+        pdl = (e != nullptr && e[0] == '0') ? 0 : 1;              // the previous kernel); B200_PDL_SKINNY=0 for A/B runs
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = (e != nullptr && e[0] == '1') ? 2 : 1;      // PDL is opt-in (see common.cuh)
+    cfg.numAttrs = pdl ? 2 : 1;
     B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tW, tX, p));
     return 0;
 }

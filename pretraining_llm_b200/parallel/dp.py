@@ -41,7 +41,7 @@ class BucketPlan:
     end: int
     chunk: int            # elements owned by each rank (last rank may own fewer)
     slot_end: List[int]   # ascending element END offsets of the slots in the bucket
-    slot_fp32: List[int]  # 1 if consumers read this slot in fp32 (must be pushed in fp32 too)
+    slot_fp32: List[int]  # 0 bf16 push only | 1 consumers read fp32: push fp32 too | 2 no push (rows read from the owner)
 
     def slice_of(self, rank: int) -> Tuple[int, int]:
         s = min(self.end, self.start + rank * self.chunk)
@@ -49,7 +49,11 @@ class BucketPlan:
         return s, e - s
 
 
-def plan_buckets(layout: ParamLayout, world: int, vocab_parallel: bool = False) -> List[BucketPlan]:
+_OWNER_READ = ("token_embed.weight", "position_embed.weight")
+
+
+def plan_buckets(layout: ParamLayout, world: int, vocab_parallel: bool = False, shard_embed: bool = False
+                 ) -> List[BucketPlan]:
     """Static ownership map: bucket b's elements [start + r*chunk, start + (r+1)*chunk) belong to rank r.
     With a vocab-parallel LM head, lm_head.weight / lm_head.bias are owned by vocabulary slice instead
     (parallel/vp.py) and leave the head bucket."""
@@ -66,7 +70,7 @@ def plan_buckets(layout: ParamLayout, world: int, vocab_parallel: bool = False) 
         for i, s in enumerate(inside):
             nxt = inside[i + 1].offset if i + 1 < len(inside) else end
             slot_end.append(nxt)
-            slot_fp32.append(0 if s.name.endswith(_BF16_ONLY) else 1)
+            slot_fp32.append(2 if (shard_embed and s.name in _OWNER_READ) else (0 if s.name.endswith(_BF16_ONLY) else 1))
         plans.append(BucketPlan(name, start, end, chunk, slot_end, slot_fp32))
     return plans
 
@@ -89,7 +93,9 @@ class DataParallel:
         lay: ParamLayout = eng.layout
         dev = eng.device
         n = lay.total
-        self.plans = plan_buckets(lay, self.world, vocab_parallel)
+        # embedding tables stay with their owners (embed_fwd reads rows over NVLink) unless B200_DP_SHARD_EMBED=0
+        self.shard_embed = self.world > 1 and os.environ.get("B200_DP_SHARD_EMBED", "1") == "1"
+        self.plans = plan_buckets(lay, self.world, vocab_parallel, self.shard_embed)
         self.nb = len(self.plans)
         self.index: Dict[str, int] = {p.name: i for i, p in enumerate(self.plans)}
         # ---- symmetric buffers: gradients, bf16 weights, fp32 masters, signal pad
@@ -99,8 +105,11 @@ class DataParallel:
         self.sym_sig = SymmBuffer(2 * self.world * self.nb * 4, self.rank, self.world, dev, multicast=False)
         # NVSwitch multicast mappings of the three buffers (all or none): the reduce kernel then pulls with
         # multimem.ld_reduce and pushes with multimem.st
+        # Measured on 8 x B200 (GPT-2-small-shaped step): 16.88 ms with multimem vs 17.35 ms with per-peer loads/stores;
+        # at 2 GPUs the switch adds latency for nothing to reduce (17.03 vs 16.64 ms): default on from 4 ranks.
         mcs = (self.sym_grad.mc_ptr, self.sym_wb.mc_ptr, self.sym_flat.mc_ptr)
-        self.multicast = all(mcs) and os.environ.get("B200_DP_MULTIMEM", "1") == "1"
+        want = os.environ.get("B200_DP_MULTIMEM", "auto")
+        self.multicast = all(mcs) and (want == "1" or (want == "auto" and self.world >= 4))
         self.mc_ptrs = tuple(ctypes.c_void_p(p) for p in mcs) if self.multicast else (None, None, None)
         new_flat = self.sym_flat.view(F32)[:n]
         new_flat.copy_(eng.flat)
@@ -135,6 +144,10 @@ class DataParallel:
         for p in self.plans:
             k = len(p.slot_end)
             self._slot_arrays.append(((ctypes.c_longlong * k)(*p.slot_end), (ctypes.c_int * k)(*p.slot_fp32), k))
+        # rank r's fp32 master slice of the embedding bucket, as every rank addresses it
+        pe = self.plans[self.index["embed"]]
+        self._emb_array = (ctypes.c_void_p * self.world)(*[self.sym_flat.ptrs[r] + 4 * (pe.start + r * pe.chunk)
+                                                            for r in range(self.world)])
         self.vp = None
         if vocab_parallel and self.world > 1:
             from .vp import VocabParallelHead
@@ -189,10 +202,26 @@ class DataParallel:
         self._launched = set()
 
     def gather_weights(self) -> None:
-        """Make the local bf16 weights complete (vocab-parallel LM head: all-gather its slices); replicated weights
-        already are."""
+        """Make the local weights complete: vocab-parallel LM head slices, and the fp32 embedding tables when they are
+        kept with their owners (off the hot path: before generation, evaluation with the plain kernels, checkpoints)."""
         if self.vp is not None:
             self.vp.gather_full(with_moments=False)
+        if self.shard_embed:
+            torch.cuda.synchronize()
+            b = self.index["embed"]
+            self._gather_bucket(b, self.eng.flat[self.owned[b][0]:self.owned[b][0] + self.owned[b][1]], self.eng.flat)
+
+    def embed_fwd(self, idx: torch.Tensor, out: torch.Tensor) -> None:
+        """Token + position embedding with every fp32 row read from the rank that owns (and updates) it."""
+        lay = self.eng.layout
+        B, T = idx.shape
+        p = self.plans[self.index["embed"]]
+        rc = lib.load().b200_embed_fwd_sharded(idx.data_ptr(), self._emb_array, self.world, p.chunk,
+                                               lay.slots["token_embed.weight"].offset - p.start,
+                                               lay.slots["position_embed.weight"].offset - p.start, out.data_ptr(), B, T,
+                                               lay.d, lay.V, torch.cuda.current_stream().cuda_stream)
+        lib.check(rc, "embed_fwd_sharded")
+        ops.LAUNCHES += 1
 
     def begin_step(self) -> None:
         """First thing of a step (main stream): advance the device-side epoch."""
@@ -204,15 +233,19 @@ class DataParallel:
             raise RuntimeError("data-parallel kernel timed out waiting for a peer (a rank died or diverged)")
 
     # ------------------------------------------------------------------ full state for checkpoints
+    def _gather_bucket(self, b: int, loc: torch.Tensor, out_flat: torch.Tensor) -> None:
+        p = self.plans[b]
+        pad = torch.zeros(p.chunk, device=loc.device, dtype=loc.dtype)
+        pad[:loc.numel()] = loc
+        parts = [torch.empty_like(pad) for _ in range(self.world)]
+        dist.all_gather(parts, pad)
+        for r, part in enumerate(parts):
+            s, cnt = p.slice_of(r)
+            out_flat[s:s + cnt] = part[:cnt]
+
     def _gather(self, local_slices: List[torch.Tensor], out_flat: torch.Tensor) -> None:
-        for p, loc in zip(self.plans, local_slices):
-            pad = torch.zeros(p.chunk, device=loc.device, dtype=loc.dtype)
-            pad[:loc.numel()] = loc
-            parts = [torch.empty_like(pad) for _ in range(self.world)]
-            dist.all_gather(parts, pad)
-            for r, part in enumerate(parts):
-                s, cnt = p.slice_of(r)
-                out_flat[s:s + cnt] = part[:cnt]
+        for b, loc in enumerate(local_slices):
+            self._gather_bucket(b, loc, out_flat)
 
     def gather_full_state(self) -> None:
         """Make fp32 masters complete on every rank and materialise full moments in eng.exp_avg(_sq).

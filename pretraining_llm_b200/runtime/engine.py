@@ -213,6 +213,8 @@ class Engine:
         lay = self.layout
         if self.store is not None:         # sharded fp32 tables: rows come from their owners over NVLink
             self.store.embed_fwd(w.idx, w.resid_a[0])
+        elif self.dp is not None and getattr(self.dp, "shard_embed", False):
+            self.dp.embed_fwd(w.idx, w.resid_a[0])     # replicated mode: the tables alone stay with their owners
         else:
             ops.embed_fwd(w.idx, self.P("token_embed.weight"), self.P("position_embed.weight"), out=w.resid_a[0])
         self._blocks_forward(w)

@@ -110,3 +110,53 @@ def test_bucket_plan_property_random_models():
         assert covered == lay.total - excluded
 
     check()
+
+
+# ---------------------------------------------------------------------------------------------- sharded mode plan
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("shape", [(4, 256, 128, 1000, 3), (12, 768, 1024, 50304, 12), (16, 2048, 2048, 50304, 24)])
+def test_zero_plan_partitions_every_bucket(world, shape):
+    """parallel/zero.py ZeroPlan: the owned slices tile every bucket exactly, every slice is 16-byte aligned in fp32
+    and bf16, shard offsets are the same on every rank, and each parameter lands either in the small replicated
+    store or in a sharded bucket (never both for the big tables)."""
+    from pretraining_llm_b200.models.layout import ParamLayout
+    from pretraining_llm_b200.parallel.zero import ZeroPlan, _NOT_SMALL
+    H, d, ctx, V, L = shape
+    lay = ParamLayout(H, d, ctx, V, L)
+    plan = ZeroPlan(lay, world)
+    assert plan.names[0] == "head" and plan.names[-1] == "embed" and plan.nb == L + 2
+    covered = 0
+    for b in range(plan.nb):
+        pos = 0
+        for r in range(world):
+            lo, cnt = plan.owned(b, r)
+            assert lo == min(plan.size(b), pos) and lo % 8 == 0 and cnt % 4 == 0 and cnt <= plan.chunk[b]
+            pos += cnt
+        assert pos == plan.size(b)
+        assert plan.chunk[b] % 128 == 0 and plan.chunk[b] * world >= plan.size(b)
+        covered += plan.size(b)
+        ends, smalls = plan.slot_tables(b)
+        assert ends == sorted(ends) and ends[-1] == plan.size(b) and len(ends) <= 16
+        inside = [s for s in lay.slots.values() if plan.start[b] <= s.offset < plan.end[b]]
+        for sl, so in zip(inside, smalls):
+            small = sl.name in plan.small_off
+            assert (so != _NOT_SMALL) == small
+            if small:      # bucket offset + so == offset in the small store
+                assert (sl.offset - plan.start[b]) + so == plan.small_off[sl.name]
+    assert covered == lay.total
+    assert plan.shard_elems == sum(plan.chunk)
+    assert "token_embed.weight" not in plan.small_off and "lm_head.weight" not in plan.small_off
+    assert "lm_head.bias" in plan.small_off and "attn_blocks.0.ln1.weight" in plan.small_off
+    offs = sorted((o, lay.slots[n].numel) for n, o in plan.small_off.items())
+    for (o1, n1), (o2, _) in zip(offs, offs[1:]):
+        assert o1 + n1 <= o2                     # no overlap in the small store
+
+
+def test_zero_plan_memory_at_1p3b_on_8_ranks():
+    from pretraining_llm_b200.models.layout import ParamLayout
+    from pretraining_llm_b200.parallel.zero import ZeroPlan
+    plan = ZeroPlan(ParamLayout(16, 2048, 2048, 50304, 24), 8)
+    per_rank = plan.bytes_per_rank()
+    assert sum(per_rank.values()) < 6e9
+    replicated = 10 * plan.layout.total + 8 * plan.layout.total // 8      # what the replicated mode holds
+    assert sum(per_rank.values()) < 0.35 * replicated
