@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--dp-mode", default="ddp", choices=["ddp", "zero"])
     ap.add_argument("--vocab-parallel", action="store_true")
+    ap.add_argument("--force-dp", action="store_true",
+                    help="diagnostic: attach the data-parallel machinery even with one rank (side stream, flags, fused "
+                         "reduce+AdamW kernels without any NVLink traffic)")
     ap.add_argument("--no-dp-check", action="store_true",
                     help="N>1: skip the untimed multi-GPU correctness check against a single-GPU engine on rank 0")
     return ap.parse_args()
@@ -201,7 +204,7 @@ def run_ours(args):
     model = Transformer(m["n_head"], m["n_embed"], T, V, N_BLOCKS=m["n_blocks"]).to(dev)
     eng = model.engine
     mode = "single"
-    if world > 1:
+    if world > 1 or args.force_dp:
         from pretraining_llm_b200.parallel import make_data_parallel
         ctx = DistContext(rank=rank, local_rank=local, world=world, device=dev)
         make_data_parallel(eng, ctx, args.dp_mode, args.vocab_parallel)

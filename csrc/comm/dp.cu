@@ -69,7 +69,7 @@ struct DpSlots {                 // slots of the bucket: element END offsets (as
 // MC = true: the buffers are bound into NVSwitch multicast objects.  The pull is ONE multimem.ld_reduce per 16 bytes
 // (the switch adds the W copies) instead of W peer loads, and each push is ONE multimem.st the switch replicates
 // instead of W peer stores: NVLink carries 1/W-th of the reduce traffic into this GPU and one copy out of it.
-template <int W, bool MC>
+template <int W, bool MC, int UMC>
 __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int rank, int bucket, int nb, const int* __restrict__ epoch_dev,
                                                               long long start, long long n, float* __restrict__ m,
                                                               float* __restrict__ v, const float* __restrict__ hyper,
@@ -97,58 +97,76 @@ __global__ void __launch_bounds__(512) dp_reduce_adamw_kernel(DpPeers P, int ran
                 bc2s = hyper[5], eps = hyper[6], gs = hyper[7];
     float* p_master = P.flat[rank];
     const long long n4 = n >> 2;  // slices are multiples of 4 elements
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4;
-         i += (long long)gridDim.x * blockDim.x) {
-        const long long e = start + i * 4;
-        // ---- 2. pull + reduce (all W loads in flight before the first add)
-        float4 s;
-        if (MC) {
-            s = multimem_ld_reduce_add_f4(P.mc_grad + e);
-        } else {
-            float4 g[W];
+    // U independent 16-byte pulls in flight per thread before the first use: a multimem.ld_reduce comes back after a
+    // switch round trip (~4-5 us), so one load per thread leaves NVLink latency-bound (148 x 512 x 16 B = 1.2 MB in flight
+    // against ~2-3 MB of bandwidth-delay product).  The per-peer path already has W loads per thread in flight.
+    constexpr int U = MC ? UMC : (W <= 2 ? 4 : (W == 4 ? 2 : 1));
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long base = blockIdx.x * (long long)blockDim.x + threadIdx.x; base < n4; base += stride * U) {
+        float4 sum[U];
+        // ---- 2. pull + reduce
 #pragma unroll
-            for (int r = 0; r < W; ++r) g[r] = ldg_stream_f4(reinterpret_cast<const float4*>(P.grad[r] + e));
-            s = g[0];
+        for (int u = 0; u < U; ++u) {
+            const long long i = base + u * stride;
+            if (i < n4) {
+                const long long e = start + i * 4;
+                if (MC) {
+                    sum[u] = multimem_ld_reduce_add_f4(P.mc_grad + e);
+                } else {
+                    float4 g[W];
 #pragma unroll
-            for (int r = 1; r < W; ++r) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+                    for (int r = 0; r < W; ++r) g[r] = ldg_stream_f4(reinterpret_cast<const float4*>(P.grad[r] + e));
+                    float4 s = g[0];
+#pragma unroll
+                    for (int r = 1; r < W; ++r) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+                    sum[u] = s;
+                }
+            }
         }
-        // ---- 3. AdamW on the owned slice (same operation order as adamw.cu)
-        float4 pv = *reinterpret_cast<float4*>(p_master + e);
-        float4 mv = reinterpret_cast<float4*>(m)[i];
-        float4 vv = reinterpret_cast<float4*>(v)[i];
-        float* pe = &pv.x; float* me = &mv.x; float* ve = &vv.x; const float* se = &s.x;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float gk = se[k] * gs;
-            pe[k] = pe[k] * decay;
-            me[k] = fmaf(w1, gk - me[k], me[k]);
-            ve[k] = fmaf(w2 * gk, gk, ve[k] * b2);
-            const float denom = __fdiv_rn(__fsqrt_rn(ve[k]), bc2s) + eps;
-            pe[k] = fmaf(-step_size, __fdiv_rn(me[k], denom), pe[k]);
-        }
-        reinterpret_cast<float4*>(m)[i] = mv;
-        reinterpret_cast<float4*>(v)[i] = vv;
-        // ---- 4. push to every rank (own copy included)
-        int need32 = 0;
+        for (int u = 0; u < U; ++u) {
+            const long long i = base + u * stride;
+            if (i >= n4) break;
+            const long long e = start + i * 4;
+            const float4 s = sum[u];
+            // ---- 3. AdamW on the owned slice (same operation order as adamw.cu)
+            float4 pv = *reinterpret_cast<float4*>(p_master + e);
+            float4 mv = reinterpret_cast<float4*>(m)[i];
+            float4 vv = reinterpret_cast<float4*>(v)[i];
+            float* pe = &pv.x; float* me = &mv.x; float* ve = &vv.x; const float* se = &s.x;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float gk = se[k] * gs;
+                pe[k] = pe[k] * decay;
+                me[k] = fmaf(w1, gk - me[k], me[k]);
+                ve[k] = fmaf(w2 * gk, gk, ve[k] * b2);
+                const float denom = __fdiv_rn(__fsqrt_rn(ve[k]), bc2s) + eps;
+                pe[k] = fmaf(-step_size, __fdiv_rn(me[k], denom), pe[k]);
+            }
+            reinterpret_cast<float4*>(m)[i] = mv;
+            reinterpret_cast<float4*>(v)[i] = vv;
+            // ---- 4. push to every rank (own copy included)
+            int need32 = 0;
 #pragma unroll 4
-        for (int k = 0; k < slots.n; ++k) {
-            if (e < slots.end[k]) { need32 = slots.fp32[k]; break; }
-        }
-        const uint2 pb = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
-        *reinterpret_cast<float4*>(p_master + e) = pv;
-        if (need32 == 2) {
-            // embedding tables: nobody consumes a bf16 copy, and embed_fwd reads the fp32 rows from their OWNER over
-            // NVLink (b200_embed_fwd_sharded) - nothing to push.  This is the bucket backward finishes last, so its
-            // reduce is the exposed one: no 206 MB of outgoing stores behind the last backward kernel.
-            *reinterpret_cast<uint2*>(P.wb[rank] + e) = pb;
-        } else if (MC) {
-            multimem_st_bf16x4(P.mc_wb + e, pb);
-            if (need32) multimem_st_f4(P.mc_flat + e, pv);
-        } else {
+            for (int k = 0; k < slots.n; ++k) {
+                if (e < slots.end[k]) { need32 = slots.fp32[k]; break; }
+            }
+            const uint2 pb = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+            *reinterpret_cast<float4*>(p_master + e) = pv;
+            if (need32 == 2) {
+                // embedding tables: nobody consumes a bf16 copy, and embed_fwd reads the fp32 rows from their OWNER over
+                // NVLink (b200_embed_fwd_sharded) - nothing to push.  This is the bucket backward finishes last, so its
+                // reduce is the exposed one: no 206 MB of outgoing stores behind the last backward kernel.
+                *reinterpret_cast<uint2*>(P.wb[rank] + e) = pb;
+            } else if (MC) {
+                multimem_st_bf16x4(P.mc_wb + e, pb);
+                if (need32) multimem_st_f4(P.mc_flat + e, pv);
+            } else {
 #pragma unroll
-            for (int r = 0; r < W; ++r) {
-                *reinterpret_cast<uint2*>(P.wb[r] + e) = pb;
-                if (need32 && r != rank) *reinterpret_cast<float4*>(P.flat[r] + e) = pv;
+                for (int r = 0; r < W; ++r) {
+                    *reinterpret_cast<uint2*>(P.wb[r] + e) = pb;
+                    if (need32 && r != rank) *reinterpret_cast<float4*>(P.flat[r] + e) = pv;
+                }
             }
         }
     }
@@ -202,12 +220,20 @@ extern "C" int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void
         threads = e ? atoi(e) : 512;
         if (threads < 32 || threads > 512 || threads % 32) threads = 512;
     }
+    static int unroll = 0;     // multimem pulls in flight per thread: 4 (default) or 1 (B200_DP_UNROLL=1, for A/B runs)
+    if (unroll == 0) {
+        const char* e = getenv("B200_DP_UNROLL");
+        unroll = (e != nullptr && atoi(e) == 1) ? 1 : 4;
+    }
 #define DP_LAUNCH(W_)                                                                                            \
-    if (mc)                                                                                                      \
-        B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_, true>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
+    if (mc && unroll > 1)                                                                                        \
+        B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_, true, 4>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
+                                    (unsigned int*)cta_counter, err));                               \
+    else if (mc)                                                                                                 \
+        B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_, true, 1>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
                                     (unsigned int*)cta_counter, err));                               \
     else                                                                                                         \
-        B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_, false>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
+        B200_CHECK_CUDA(b200_launch(dp_reduce_adamw_kernel<W_, false, 1>, dim3(ctas), dim3(threads), 0, st, P, rank, bucket, num_buckets, epoch_dev, start, n, m, v, hyper, S, \
                                     (unsigned int*)cta_counter, err))
     switch (world) {
         case 1: DP_LAUNCH(1); break;

@@ -34,7 +34,7 @@ struct ZrSlots {                       // parameter slots of the bucket, offsets
 };
 #define ZR_NOT_SMALL (-(1ll << 62))
 
-template <int W, bool MC>
+template <int W, bool MC, int UMC>
 __global__ void __launch_bounds__(512) zero_reduce_adamw_kernel(ZrPeers P, int rank, int bucket, int nb,
                                                                 const int* __restrict__ epoch_dev, long long lo, long long n,
                                                                 float* __restrict__ master, float* __restrict__ m,
@@ -59,47 +59,64 @@ __global__ void __launch_bounds__(512) zero_reduce_adamw_kernel(ZrPeers P, int r
     const float decay = hyper[0], b2 = hyper[1], w1 = hyper[2], w2 = hyper[3], step_size = hyper[4],
                 bc2s = hyper[5], eps = hyper[6], gs = hyper[7];
     const long long n4 = n >> 2;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
-        const long long e = lo + i * 4;                 // offset inside the bucket
-        float4 s;
-        if (MC) {
-            s = multimem_ld_reduce_add_f4(P.mc_grad + e);
-        } else {
-            float4 g[W];
+    // U independent pulls in flight per thread (see dp.cu: a multimem.ld_reduce is a switch round trip away)
+    constexpr int U = MC ? UMC : (W <= 2 ? 4 : (W == 4 ? 2 : 1));
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long base = blockIdx.x * (long long)blockDim.x + threadIdx.x; base < n4; base += stride * U) {
+        float4 sum[U];
 #pragma unroll
-            for (int r = 0; r < W; ++r) g[r] = ldg_stream_f4(reinterpret_cast<const float4*>(P.grad[r] + e));
-            s = g[0];
+        for (int u = 0; u < U; ++u) {
+            const long long i = base + u * stride;
+            if (i < n4) {
+                const long long e = lo + i * 4;             // offset inside the bucket
+                if (MC) {
+                    sum[u] = multimem_ld_reduce_add_f4(P.mc_grad + e);
+                } else {
+                    float4 g[W];
 #pragma unroll
-            for (int r = 1; r < W; ++r) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+                    for (int r = 0; r < W; ++r) g[r] = ldg_stream_f4(reinterpret_cast<const float4*>(P.grad[r] + e));
+                    float4 s = g[0];
+#pragma unroll
+                    for (int r = 1; r < W; ++r) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+                    sum[u] = s;
+                }
+            }
         }
-        float4 pv = reinterpret_cast<float4*>(master)[i];
-        float4 mv = reinterpret_cast<float4*>(m)[i];
-        float4 vv = reinterpret_cast<float4*>(v)[i];
-        float* pe = &pv.x; float* me = &mv.x; float* ve = &vv.x; const float* se = &s.x;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {                   // same operation order as adamw.cu
-            const float gk = se[k] * gs;
-            pe[k] = pe[k] * decay;
-            me[k] = fmaf(w1, gk - me[k], me[k]);
-            ve[k] = fmaf(w2 * gk, gk, ve[k] * b2);
-            const float denom = __fdiv_rn(__fsqrt_rn(ve[k]), bc2s) + eps;
-            pe[k] = fmaf(-step_size, __fdiv_rn(me[k], denom), pe[k]);
-        }
-        reinterpret_cast<float4*>(master)[i] = pv;
-        reinterpret_cast<float4*>(m)[i] = mv;
-        reinterpret_cast<float4*>(v)[i] = vv;
-        reinterpret_cast<uint2*>(shard16)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
-        long long so = ZR_NOT_SMALL;
+        for (int u = 0; u < U; ++u) {
+            const long long i = base + u * stride;
+            if (i >= n4) break;
+            const long long e = lo + i * 4;
+            const float4 s = sum[u];
+            float4 pv = reinterpret_cast<float4*>(master)[i];
+            float4 mv = reinterpret_cast<float4*>(m)[i];
+            float4 vv = reinterpret_cast<float4*>(v)[i];
+            float* pe = &pv.x; float* me = &mv.x; float* ve = &vv.x; const float* se = &s.x;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {                   // same operation order as adamw.cu
+                const float gk = se[k] * gs;
+                pe[k] = pe[k] * decay;
+                me[k] = fmaf(w1, gk - me[k], me[k]);
+                ve[k] = fmaf(w2 * gk, gk, ve[k] * b2);
+                const float denom = __fdiv_rn(__fsqrt_rn(ve[k]), bc2s) + eps;
+                pe[k] = fmaf(-step_size, __fdiv_rn(me[k], denom), pe[k]);
+            }
+            reinterpret_cast<float4*>(master)[i] = pv;
+            reinterpret_cast<float4*>(m)[i] = mv;
+            reinterpret_cast<float4*>(v)[i] = vv;
+            reinterpret_cast<uint2*>(shard16)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+            long long so = ZR_NOT_SMALL;
 #pragma unroll 4
-        for (int k = 0; k < slots.n; ++k) {
-            if (e < slots.end[k]) { so = slots.small_off[k]; break; }
-        }
-        if (so != ZR_NOT_SMALL) {                       // LayerNorm / bias parameter: every rank reads it in fp32
-            if (MC) {
-                multimem_st_f4(P.mc_small + (e + so), pv);
-            } else {
+            for (int k = 0; k < slots.n; ++k) {
+                if (e < slots.end[k]) { so = slots.small_off[k]; break; }
+            }
+            if (so != ZR_NOT_SMALL) {                       // LayerNorm / bias parameter: every rank reads it in fp32
+                if (MC) {
+                    multimem_st_f4(P.mc_small + (e + so), pv);
+                } else {
 #pragma unroll
-                for (int r = 0; r < W; ++r) *reinterpret_cast<float4*>(P.small[r] + (e + so)) = pv;
+                    for (int r = 0; r < W; ++r) *reinterpret_cast<float4*>(P.small[r] + (e + so)) = pv;
+                }
             }
         }
     }
@@ -175,10 +192,10 @@ extern "C" int b200_zero_reduce_adamw(void* const* h_grad, void* mc_grad, void* 
     for (int k = 0; k < n_slots; ++k) { S.end[k] = h_slot_end[k]; S.small_off[k] = h_slot_small_off[k]; }
 #define ZR_LAUNCH(W_)                                                                                               \
     if (mc)                                                                                                         \
-        B200_CHECK_CUDA(b200_launch(zero_reduce_adamw_kernel<W_, true>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, \
+        B200_CHECK_CUDA(b200_launch(zero_reduce_adamw_kernel<W_, true, 4>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, \
                                     epoch_dev, lo, n, master, m, v, (bf16*)shard16, hyper, S, (unsigned int*)cta_counter, err)); \
     else                                                                                                            \
-        B200_CHECK_CUDA(b200_launch(zero_reduce_adamw_kernel<W_, false>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, \
+        B200_CHECK_CUDA(b200_launch(zero_reduce_adamw_kernel<W_, false, 1>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, \
                                     epoch_dev, lo, n, master, m, v, (bf16*)shard16, hyper, S, (unsigned int*)cta_counter, err))
     switch (world) {
         case 1: ZR_LAUNCH(1); break;

@@ -85,3 +85,45 @@ extern "C" int b200_embed_bwd(const long long* idx, const float* dx, float* dwte
     B200_CHECK_CUDA(b200_launch(embed_bwd_pos_kernel, dim3(max(blocks2, 1)), dim3(256), 0, st, dx, dwpe, B, T, d, accumulate));
     B200_RETURN_LAUNCH_STATUS("embed_bwd");
 }
+
+
+// Deterministic token-embedding gradient (B200_DETERMINISTIC=1 in the engine): `order` is a STABLE argsort of the token
+// ids (torch.sort), so equal tokens sit next to each other in position order.  One warp per position p that starts a
+// run (sorted token differs from its predecessor) sums the run's dx rows in that fixed order and writes - not adds -
+// the row, so the result does not depend on the order in which atomics land.  dwte must be zero (or hold the running
+// sum when accumulate != 0) for the rows no token touches / before the add.
+__global__ void __launch_bounds__(256) embed_bwd_tok_sorted_kernel(const long long* __restrict__ idx,
+                                                                   const long long* __restrict__ order,
+                                                                   const float* __restrict__ dx, float* __restrict__ dwte,
+                                                                   int M, int d, int V, int accumulate) {
+    pdl_sync();
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int p = warp; p < M; p += nwarps) {
+        const long long tok = idx[order[p]];
+        if (p > 0 && idx[order[p - 1]] == tok) continue;          // not the start of a run
+        const long long row = tok < 0 ? 0 : (tok >= V ? V - 1 : tok);
+        float* o = dwte + (size_t)row * d;
+        for (int c = lane; c < d / 4; c += 32) {
+            float4 acc = accumulate ? reinterpret_cast<const float4*>(o)[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int q = p; q < M && idx[order[q]] == tok; ++q) {
+                const float4 v = ldg_stream_f4(reinterpret_cast<const float4*>(dx + (size_t)order[q] * d) + c);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            reinterpret_cast<float4*>(o)[c] = acc;
+        }
+    }
+}
+
+extern "C" int b200_embed_bwd_sorted(const long long* idx, const long long* order, const float* dx, float* dwte, float* dwpe,
+                                     int B, int T, int d, int V, int accumulate, cudaStream_t st) {
+    B200_REQUIRE(d % 4 == 0, "embed_bwd_sorted: d must be a multiple of 4");
+    const int M = B * T;
+    const int blocks = min((M + 7) / 8, b200_num_sms() * 8);
+    B200_CHECK_CUDA(b200_launch(embed_bwd_tok_sorted_kernel, dim3(max(blocks, 1)), dim3(256), 0, st, idx, order, dx, dwte, M, d, V,
+                                accumulate));
+    const int total4 = T * d / 4;
+    const int blocks2 = min((total4 + 255) / 256, b200_num_sms() * 8);
+    B200_CHECK_CUDA(b200_launch(embed_bwd_pos_kernel, dim3(max(blocks2, 1)), dim3(256), 0, st, dx, dwpe, B, T, d, accumulate));
+    B200_RETURN_LAUNCH_STATUS("embed_bwd_sorted");
+}

@@ -119,3 +119,13 @@ extern "C" int b200_l2_flush(void* buf, long long bytes, cudaStream_t st) {
     B200_CHECK_CUDA(b200_launch(fill_kernel, dim3(b200_num_sms() * 8), dim3(256), 0, st, (float4*)buf, bytes / 16, 0.f));
     B200_RETURN_LAUNCH_STATUS("l2_flush");
 }
+
+
+// Zero-fill as a memset node (DMA engine, capturable): what the training step uses for the scatter-add target of the
+// embedding gradient and the loss accumulator, so that a captured step contains this library's kernels and memset
+// nodes only.
+extern "C" int b200_memset_zero(void* ptr, long long bytes, cudaStream_t st) {
+    if (bytes <= 0) return 0;
+    B200_CHECK_CUDA(cudaMemsetAsync(ptr, 0, (size_t)bytes, st));
+    return 0;
+}

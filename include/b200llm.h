@@ -30,6 +30,8 @@ int b200_cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t st)
 /* out[N] (+)= column sums of bf16 a[M,N] (bias gradients; ref: autograd of nn.Linear bias, mlp.py:24-26) */
 int b200_colsum_bf16(const void* a, float* out, int M, int N, int ld, int accumulate, cudaStream_t st);
 int b200_l2_flush(void* buf, long long bytes, cudaStream_t st);
+/* zero-fill as a memset node (capturable; no kernel) */
+int b200_memset_zero(void* ptr, long long bytes, cudaStream_t st);
 
 /* ---- embedding (ref: src/models/transformer.py:51-54) -------------------------------------- */
 /* x[b*T+t, :] = wte[idx[b,t], :] + wpe[pos0 + t, :]   (fp32) */
@@ -37,6 +39,10 @@ int b200_embed_fwd(const long long* idx, const float* wte, const float* wpe, flo
 /* dwte[idx[m], :] += dx[m, :] (vector RED; caller zeroes dwte on the first micro-step);
  * dwpe[t, :] (+)= sum_b dx[b, t, :] */
 int b200_embed_bwd(const long long* idx, const float* dx, float* dwte, float* dwpe, int B, int T, int d, int V, int accumulate, cudaStream_t st);
+
+/* Deterministic variant: `order` = stable argsort of idx (device, int64 [B*T]); runs of equal tokens are summed in
+ * position order by one warp and the row is written once - no floating-point atomics, bit-identical run to run. */
+int b200_embed_bwd_sorted(const long long* idx, const long long* order, const float* dx, float* dwte, float* dwpe, int B, int T, int d, int V, int accumulate, cudaStream_t st);
 
 /* ---- fused residual-add + LayerNorm (ref: src/models/transformer_block.py:44,46; transformer.py:70) */
 int b200_ln_supported(int d);

@@ -161,6 +161,23 @@ def embed_bwd(idx, dx, dwte, dwpe, accumulate: bool = False):
          "embed_bwd")
 
 
+def embed_bwd_sorted(idx, order, dx, dwte, dwpe, accumulate: bool = False):
+    """Deterministic embedding backward: `order` is a stable argsort of idx.view(-1)."""
+    B, T = idx.shape
+    V, d = dwte.shape
+    _chk(lib.load().b200_embed_bwd_sorted(_p(idx), _p(order), _p(dx), _p(dwte), _p(dwpe), B, T, d, V, int(accumulate), _st()),
+         "embed_bwd")
+
+
+def zero_(t: torch.Tensor) -> torch.Tensor:
+    """Zero a contiguous tensor with a memset node (no kernel launch; capturable)."""
+    assert t.is_contiguous()
+    rc = lib.load().b200_memset_zero(_p(t), t.numel() * t.element_size(), _st())
+    if rc != 0:
+        lib.check(rc, "memset_zero")
+    return t
+
+
 def ln_fwd(x, gamma, beta, *, branch=None, x_out=None, out=None, out_f32=None, mean=None, rstd=None,
            eps: float = 1e-5, want_stats: bool = True):
     """r = x (+ branch -> stored to x_out, default in place) -> bf16 LN(r) (+ mean, rstd)."""

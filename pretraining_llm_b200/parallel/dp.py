@@ -113,7 +113,8 @@ class DataParallel:
         self.mc_ptrs = tuple(ctypes.c_void_p(p) for p in mcs) if self.multicast else (None, None, None)
         new_flat = self.sym_flat.view(F32)[:n]
         new_flat.copy_(eng.flat)
-        dist.broadcast(new_flat, src=0)                   # identical replicas to start from
+        if self.world > 1:
+            dist.broadcast(new_flat, src=0)               # identical replicas to start from
         model = eng.model
         with torch.no_grad():
             for name, p in model.named_parameters():
@@ -154,7 +155,8 @@ class DataParallel:
             self.vp = VocabParallelHead(eng, self)
         if eng.exp_avg is not None:        # moments loaded before the ranks were attached (resume): keep the owned slices
             self.state_loaded()
-        dist.barrier()
+        if self.world > 1:
+            dist.barrier()
         torch.cuda.synchronize()
 
     # ------------------------------------------------------------------ per-step protocol
@@ -238,7 +240,10 @@ class DataParallel:
         pad = torch.zeros(p.chunk, device=loc.device, dtype=loc.dtype)
         pad[:loc.numel()] = loc
         parts = [torch.empty_like(pad) for _ in range(self.world)]
-        dist.all_gather(parts, pad)
+        if self.world > 1:
+            dist.all_gather(parts, pad)
+        else:
+            parts = [pad]
         for r, part in enumerate(parts):
             s, cnt = p.slice_of(r)
             out_flat[s:s + cnt] = part[:cnt]

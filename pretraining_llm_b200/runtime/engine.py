@@ -26,6 +26,7 @@ sums).  See DESIGN.md for the buffer plan.
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -34,6 +35,9 @@ from .. import ops
 from ..utils import nvtx
 
 BF16, F32 = torch.bfloat16, torch.float32
+# B200_DETERMINISTIC=1: the token-embedding gradient is summed in a fixed order (sort by token) instead of with vector
+# fp32 atomics whose arrival order varies from run to run
+DETERMINISTIC = os.environ.get("B200_DETERMINISTIC", "0") == "1"
 
 
 class Workspace:
@@ -225,7 +229,7 @@ class Engine:
         ops.gemm(w.hf, self.W("lm_head.weight"), out=w.logits[:, :V], bias=self.P("lm_head.bias"),
                  stats=w.ce_stats if with_loss else None, bn=256)
         if with_loss:
-            w.loss.zero_()
+            ops.zero_(w.loss)
             ops.ce_finalize(w.ce_stats, w.nt, w.logits, w.tgt.view(-1), w.ce_lse, w.loss_rows, w.loss, V,
                             sum_scale=loss_scale / w.M)
 
@@ -249,7 +253,7 @@ class Engine:
                                           "gradient accumulation needs dp_mode='ddp'")
             z.begin_pass()
         if not accumulate:
-            self.G("token_embed.weight").zero_()     # scatter-add target
+            ops.zero_(self.G("token_embed.weight"))  # scatter-add target (memset node, not a fill kernel)
         # LM head + CE
         if self.dp is not None and self.dp.vp is not None:
             self.dp.vp.backward(w, grad_scale, accumulate)
@@ -292,10 +296,16 @@ class Engine:
                                  self.G(pre + "ln1.bias"), None, accumulate=accumulate)
             if dp is not None:
                 dp.bucket_ready(f"block{l}")
-        ops.embed_bwd(w.idx, w.dx, self.G("token_embed.weight"), self.G("position_embed.weight")[:T],
-                      accumulate=accumulate)
+        if DETERMINISTIC:
+            # stable sort of the token ids (torch.sort, capturable) -> runs of equal tokens summed in position order
+            order = torch.sort(w.idx.view(-1), stable=True).indices
+            ops.embed_bwd_sorted(w.idx, order, w.dx, self.G("token_embed.weight"), self.G("position_embed.weight")[:T],
+                                 accumulate=accumulate)
+        else:
+            ops.embed_bwd(w.idx, w.dx, self.G("token_embed.weight"), self.G("position_embed.weight")[:T],
+                          accumulate=accumulate)
         if not accumulate and T < lay.ctx:
-            self.G("position_embed.weight")[T:].zero_()
+            ops.zero_(self.G("position_embed.weight")[T:])
 
     # ------------------------------------------------------------------ optimizer
     def set_hyper(self, lr: float, grad_scale: float = 1.0) -> None:

@@ -299,3 +299,26 @@ def test_loss_overlay_vs_reference_module(ref_models):
         last = lo
     assert worst < 0.05, worst
     assert last < first - 1.0, (first, last)       # the curve actually moved
+
+
+def test_embed_bwd_sorted_is_deterministic_and_matches_index_add(ops):
+    """The sort-by-token embedding backward against torch index_add_, bit-identical across two runs, with the
+    accumulate form and heavy token repetition (Zipf-like ids)."""
+    torch.manual_seed(12)
+    B, T, d, V = 4, 256, 768, 5000
+    idx = (torch.rand(B, T, device="cuda") ** 4 * V).long().clamp_(0, V - 1)     # many repeats of small ids
+    dx = torch.randn(B * T, d, device="cuda")
+    order = torch.sort(idx.view(-1), stable=True).indices
+    outs = []
+    for _ in range(2):
+        dwte = torch.zeros(V, d, device="cuda")
+        dwpe = torch.zeros(T, d, device="cuda")
+        ops.embed_bwd_sorted(idx, order, dx, dwte, dwpe)
+        outs.append((dwte, dwpe))
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    ref = torch.zeros(V, d, device="cuda", dtype=torch.float64).index_add_(0, idx.view(-1), dx.double())
+    assert _rel(outs[0][0], ref) < 1e-6
+    assert _rel(outs[0][1], dx.view(B, T, d).sum(0)) < 1e-6
+    ops.embed_bwd_sorted(idx, order, dx, outs[0][0], outs[0][1], accumulate=True)
+    assert _rel(outs[0][0], 2 * ref) < 1e-6

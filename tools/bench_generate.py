@@ -25,6 +25,8 @@ ap.add_argument("--batch", type=int, default=32)
 ap.add_argument("--new", type=int, default=512)
 ap.add_argument("--prompt", type=int, default=16)
 ap.add_argument("--ref-new", type=int, default=0, help="reference only: time this many tokens and extrapolate nothing")
+ap.add_argument("--ref-autocast", action="store_true",
+                help="reference only, for information: run its generate under bf16 autocast (its script runs fp32)")
 args = ap.parse_args()
 m = MODELS[args.model]
 T, V = m["context_length"], m["vocab_size"]
@@ -41,7 +43,7 @@ else:
     R = import_reference_models()
     model = R.Transformer(m["n_head"], m["n_embed"], T, V, m["n_blocks"]).cuda().eval()
     def gen(n):
-        with torch.no_grad():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=args.ref_autocast):
             return model.generate(prompt, n)
     new = args.ref_new or args.new
 
@@ -60,5 +62,6 @@ print(json.dumps({"metric": "generation tokens/sec", "impl": args.impl, "value":
                   "unit": "tokens/s", "batch": args.batch, "new_tokens": new, "prompt": args.prompt,
                   "ms_total": ms, "ms_per_token_step": ms / new, "wall_s": wall,
                   "config": {"model": f"{args.model}-shaped decoder {m['n_blocks']}L d={m['n_embed']} H={m['n_head']} ctx={T}",
-                             "dtype": "bf16 weights/KV cache, fp32 softmax" if args.impl == "ours" else "fp32 (reference default)",
+                             "dtype": "bf16 weights/KV cache, fp32 softmax" if args.impl == "ours" else
+                             ("bf16 autocast (information only)" if args.ref_autocast else "fp32 (reference default)"),
                              "data": "random prompt, random-init weights"}}))

@@ -14,7 +14,10 @@ WANT = [
     r"attn_bwd_tc_kernel<64, true>", r"attn_bwd_tc_kernel<64, false>", r"attn_bwd_tc_kernel<128, true>",
     r"attn_bwd_tc_kernel<128, false>", r"attn_bwd_delta_tc_kernel<64>", r"ln_fwd_kernel<3, 2>", r"ln_bwd_kernel<3, 2, true>",
     r"ln_bwd_finalize2_kernel", r"adamw_kernel", r"ce_grad_kernel", r"ce_finalize_kernel", r"embed_fwd_kernel",
-    r"embed_bwd_tok_kernel", r"colsum_bf16_kernel", r"dp_reduce_adamw_kernel<8>", r"vp_ce_finalize_kernel",
+    r"embed_bwd_tok_kernel", r"embed_bwd_tok_sorted_kernel", r"colsum_bf16_kernel",
+    r"dp_reduce_adamw_kernel<8, true, 4>", r"dp_reduce_adamw_kernel<8, false, 1>", r"zero_reduce_adamw_kernel<8, true, 4>",
+    r"zero_reduce_adamw_kernel<8, false, 1>", r"zero_wait_kernel", r"embed_fwd_sharded_kernel",
+    r"gemm2_kernel<256, false, true, false, true>", r"vp_ce_finalize_kernel",
     r"vp_gather_rows_kernel", r"attn_decode_kernel<128>", r"sample_kernel",
 ]
 
