@@ -239,9 +239,20 @@ int launch_skinny(const CUtensorMap& tW, const CUtensorMap& tX, const SParams& p
 extern "C" int b200_gemm_skinny_splits(int M, int N, int K) {
     const int sms = b200_num_sms();
     const int n_tiles = (N + 127) / 128, num_kb = (K + BK - 1) / BK;
+    (void)M;
+    static int any = -1;
+    if (any < 0) {
+        const char* e = getenv("B200_SKINNY_ANY_SPLIT");       // cluster sizes 3, 5, 6, 7 as well (one CTA per SM for more shapes)
+        any = (e != nullptr && e[0] == '1') ? 1 : 0;
+    }
+    if (any) {
+        int s = sms / n_tiles;
+        s = s < 1 ? 1 : (s > 8 ? 8 : s);
+        while (s > 1 && num_kb / s < 4) --s;
+        return s;
+    }
     int splits = 1;
     while (splits < 8 && n_tiles * splits * 2 <= sms + sms / 4 && num_kb / (splits * 2) >= 4) splits *= 2;
-    (void)M;
     return splits;
 }
 
@@ -255,8 +266,8 @@ extern "C" int b200_gemm_skinny(const void* x, const void* W, void* out, int M, 
     p.M = M; p.N = N; p.K = K;
     p.num_kb = (K + BK - 1) / BK;
     p.splits = split_k > 0 ? split_k : b200_gemm_skinny_splits(M, N, K);
-    B200_REQUIRE(p.splits == 1 || p.splits == 2 || p.splits == 4 || p.splits == 8, "gemm_skinny: split_k must be 1, 2, 4 or 8");
-    while (p.splits > 1 && p.num_kb < p.splits) p.splits /= 2;
+    B200_REQUIRE(p.splits >= 1 && p.splits <= 8, "gemm_skinny: split_k must be in [1, 8] (a thread-block cluster along K)");
+    while (p.splits > 1 && p.num_kb < p.splits) --p.splits;
     p.kb_per_split = (p.num_kb + p.splits - 1) / p.splits;
     p.bias = bias; p.relu = relu; p.out = (bf16*)out; p.ldc = ldc;
     CUtensorMap tW, tX;

@@ -123,6 +123,158 @@ __global__ void __launch_bounds__(DEC_WARPS * 32) attn_decode_kernel(const bf16*
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Split-KV decode attention.  Grid (H, B, S): the S CTAs of a (batch row, head) pair each take 1/S of the cached keys,
+// so the grid has B*H*S CTAs of 4 warps however long the context is and every SM streams the cache.  A lane owns
+// HD/32 contiguous dimensions of every key / value row: all loads are coalesced (a warp reads a whole row per
+// instruction), 8 key rows and 8 value rows are in flight per warp before the first use (4 KB per warp, ~128 KB per SM
+// at 8 CTAs per SM), the dot products are completed with xor-shuffles, and the online softmax runs 8 keys at a time.
+// Partials (m, l, acc) of the splits go to `scratch`; the LAST CTA of a (b, h) pair to arrive (atomic ticket) merges
+// them and writes the output row - one launch, no second kernel.  With append != 0 the warp that meets position
+// len-1 takes that key / value row from qkv and stores it into the cache (fused KV append).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int DS_WARPS = 4;
+constexpr int DS_KB = 8;
+
+template <int HD>
+__global__ void __launch_bounds__(DS_WARPS * 32) attn_decode_split_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ kc,
+                                                                          bf16* __restrict__ vc, bf16* __restrict__ out,
+                                                                          float* __restrict__ scratch, unsigned int* tickets,
+                                                                          int H, int Tmax, int len, float scale_log2,
+                                                                          const int* __restrict__ pos_dev, int append) {
+    pdl_sync();
+    if (pos_dev != nullptr) len = *pos_dev + 1;
+    constexpr int VPL = HD / 32;                 // dimensions per lane: 2 (hs 64) or 4 (hs 128)
+    __shared__ float s_m[DS_WARPS], s_l[DS_WARPS];
+    __shared__ float s_acc[DS_WARPS][HD];
+    __shared__ unsigned int s_ticket;
+    const int h = blockIdx.x, b = blockIdx.y, sp = blockIdx.z, S = gridDim.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    bf16* kb = kc + ((size_t)b * H + h) * Tmax * HD + lane * VPL;
+    bf16* vb = vc + ((size_t)b * H + h) * Tmax * HD + lane * VPL;
+    const bf16* qrow = qkv + (size_t)b * 3 * H * HD + h * HD + lane * VPL;
+    float q[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) q[i] = __bfloat162float(qrow[i]) * scale_log2;
+
+    const int per = ((len + S - 1) / S + DS_KB - 1) / DS_KB * DS_KB;      // keys per split, a multiple of the block
+    const int lo = sp * per, hi = min(len, lo + per);
+    float m = -INFINITY, l = 0.f, acc[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) acc[i] = 0.f;
+
+    for (int j0 = lo + warp * DS_KB; j0 < hi; j0 += DS_WARPS * DS_KB) {
+        float kf[DS_KB][VPL], vf[DS_KB][VPL];
+        // ---- all 16 row loads of the block are issued before anything is used
+#pragma unroll
+        for (int i = 0; i < DS_KB; ++i) {
+            const int j = j0 + i;
+            const bool fresh = append && j == len - 1;           // this step's own key / value: from qkv, into the cache
+            const bf16* kr = fresh ? qrow + (size_t)H * HD : kb + (size_t)j * HD;
+            const bf16* vr = fresh ? qrow + 2 * (size_t)H * HD : vb + (size_t)j * HD;
+            if (j < hi) {
+                if (VPL == 2) {
+                    const uint32_t ku = *reinterpret_cast<const uint32_t*>(kr), vu = *reinterpret_cast<const uint32_t*>(vr);
+                    const float2 a = unpack_bf16x2(ku), c = unpack_bf16x2(vu);
+                    kf[i][0] = a.x; kf[i][1] = a.y; vf[i][0] = c.x; vf[i][1] = c.y;
+                    if (fresh) {
+                        *reinterpret_cast<uint32_t*>(kb + (size_t)j * HD) = ku;
+                        *reinterpret_cast<uint32_t*>(vb + (size_t)j * HD) = vu;
+                    }
+                } else {
+                    const uint2 ku = *reinterpret_cast<const uint2*>(kr), vu = *reinterpret_cast<const uint2*>(vr);
+                    const float2 a0 = unpack_bf16x2(ku.x), a1 = unpack_bf16x2(ku.y), c0 = unpack_bf16x2(vu.x), c1 = unpack_bf16x2(vu.y);
+                    kf[i][0] = a0.x; kf[i][1] = a0.y; kf[i][VPL - 2] = a1.x; kf[i][VPL - 1] = a1.y;
+                    vf[i][0] = c0.x; vf[i][1] = c0.y; vf[i][VPL - 2] = c1.x; vf[i][VPL - 1] = c1.y;
+                    if (fresh) {
+                        *reinterpret_cast<uint2*>(kb + (size_t)j * HD) = ku;
+                        *reinterpret_cast<uint2*>(vb + (size_t)j * HD) = vu;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < VPL; ++e) { kf[i][e] = 0.f; vf[i][e] = 0.f; }
+            }
+        }
+        // ---- 8 dot products: per-lane partials, then xor-shuffle butterflies (every lane ends with every score)
+        float sc[DS_KB];
+#pragma unroll
+        for (int i = 0; i < DS_KB; ++i) {
+            float d = 0.f;
+#pragma unroll
+            for (int e = 0; e < VPL; ++e) d = fmaf(kf[i][e], q[e], d);
+            sc[i] = d;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int i = 0; i < DS_KB; ++i) sc[i] += __shfl_xor_sync(0xffffffffu, sc[i], o);
+        float mx = m;
+#pragma unroll
+        for (int i = 0; i < DS_KB; ++i) {
+            if (j0 + i >= hi) sc[i] = -INFINITY;
+            mx = fmaxf(mx, sc[i]);
+        }
+        const float corr = exp2f(m - mx);                     // m = -inf on the first block: exp2(-inf) = 0
+        m = mx;
+        l *= corr;
+#pragma unroll
+        for (int e = 0; e < VPL; ++e) acc[e] *= corr;
+#pragma unroll
+        for (int i = 0; i < DS_KB; ++i) {
+            const float p = exp2f(sc[i] - mx);                // masked keys: exp2(-inf) = 0
+            l += p;
+#pragma unroll
+            for (int e = 0; e < VPL; ++e) acc[e] = fmaf(p, vf[i][e], acc[e]);
+        }
+    }
+    // ---- merge the warps of this CTA
+    if (lane == 0) { s_m[warp] = m; s_l[warp] = l; }
+#pragma unroll
+    for (int e = 0; e < VPL; ++e) s_acc[warp][lane * VPL + e] = acc[e];
+    __syncthreads();
+    float M = -INFINITY, L = 0.f, o = 0.f;
+    if (threadIdx.x < HD) {
+#pragma unroll
+        for (int w = 0; w < DS_WARPS; ++w) M = fmaxf(M, s_m[w]);
+#pragma unroll
+        for (int w = 0; w < DS_WARPS; ++w) {
+            const float f = s_m[w] == -INFINITY ? 0.f : exp2f(s_m[w] - M);
+            L += s_l[w] * f;
+            o += s_acc[w][threadIdx.x] * f;
+        }
+    }
+    bf16* orow = out + (size_t)b * H * HD + h * HD;
+    if (S == 1) {
+        if (threadIdx.x < HD) orow[threadIdx.x] = __float2bfloat16_rn(L > 0.f ? o / L : 0.f);
+        return;
+    }
+    // ---- publish this split's partial; the last split to arrive merges all of them
+    float* mine = scratch + (((size_t)b * H + h) * S + sp) * (HD + 2);
+    if (threadIdx.x < HD) mine[2 + threadIdx.x] = o;
+    if (threadIdx.x == 0) { mine[0] = M; mine[1] = L; }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_ticket = atomicAdd(tickets + b * H + h, 1u);
+    __syncthreads();
+    if (s_ticket != (unsigned int)(S - 1)) return;
+    __threadfence();
+    if (threadIdx.x < HD) {
+        const float* base = scratch + ((size_t)b * H + h) * S * (HD + 2);
+        float MM = -INFINITY;
+        for (int s2 = 0; s2 < S; ++s2) MM = fmaxf(MM, __ldcg(base + s2 * (HD + 2)));
+        float LL = 0.f, oo = 0.f;
+        for (int s2 = 0; s2 < S; ++s2) {
+            const float ms = __ldcg(base + s2 * (HD + 2));
+            const float f = ms == -INFINITY ? 0.f : exp2f(ms - MM);
+            LL += __ldcg(base + s2 * (HD + 2) + 1) * f;
+            oo += __ldcg(base + s2 * (HD + 2) + 2 + threadIdx.x) * f;
+        }
+        orow[threadIdx.x] = __float2bfloat16_rn(LL > 0.f ? oo / LL : 0.f);
+    }
+    if (threadIdx.x == 0) tickets[b * H + h] = 0;             // ready for the next launch
+}
+
 __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
     x += 0x9E3779B97F4A7C15ull;
     x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -272,4 +424,25 @@ extern "C" int b200_gather_last_rows(const void* in, void* out, int B, int T, in
     const int rc = row_bytes / 16;
     B200_CHECK_CUDA(b200_launch(gather_last_rows_kernel, dim3((B * rc + 255) / 256), dim3(256), 0, st, (const uint4*)in, (uint4*)out, B, T, rc));
     B200_RETURN_LAUNCH_STATUS("gather_last_rows");
+}
+
+
+// Split-KV form of b200_attn_decode (same contract).  scratch: B * H * splits * (hs + 2) floats; tickets: B * H zeroed
+// unsigned ints (left zero).  splits >= 1; with splits == 1 scratch / tickets may be null.
+extern "C" int b200_attn_decode_split(const void* qkv, void* kcache, void* vcache, void* out, float* scratch, void* tickets,
+                                      int B, int H, int hs, int Tmax, int len, float scale, const int* pos_dev, int append,
+                                      int splits, cudaStream_t st) {
+    B200_REQUIRE(hs == 64 || hs == 128, "attn_decode_split: head size must be 64 or 128");
+    B200_REQUIRE(len >= 1 && len <= Tmax, "attn_decode_split: bad len");
+    B200_REQUIRE(splits >= 1 && splits <= 64 && (splits == 1 || (scratch != nullptr && tickets != nullptr)),
+                 "attn_decode_split: splits > 1 needs scratch and tickets");
+    const float scale_log2 = scale * 1.4426950408889634f;
+    dim3 grid(H, B, splits);
+    if (hs == 64)
+        B200_CHECK_CUDA(b200_launch(attn_decode_split_kernel<64>, grid, dim3(DS_WARPS * 32), 0, st, (const bf16*)qkv, (bf16*)kcache,
+                                    (bf16*)vcache, (bf16*)out, scratch, (unsigned int*)tickets, H, Tmax, len, scale_log2, pos_dev, append));
+    else
+        B200_CHECK_CUDA(b200_launch(attn_decode_split_kernel<128>, grid, dim3(DS_WARPS * 32), 0, st, (const bf16*)qkv, (bf16*)kcache,
+                                    (bf16*)vcache, (bf16*)out, scratch, (unsigned int*)tickets, H, Tmax, len, scale_log2, pos_dev, append));
+    B200_RETURN_LAUNCH_STATUS("attn_decode_split");
 }

@@ -143,6 +143,10 @@ int b200_kv_append(const void* qkv, void* kcache, void* vcache, int B, int t, in
 /* single-position decode attention: q = q-third of qkv [B, 3*H*hs], attends to cache[0..len).
  * append != 0: first write this position's k / v thirds into the caches at index len-1 (fused kv_append). */
 int b200_attn_decode(const void* qkv, void* kcache, void* vcache, void* out, int B, int H, int hs, int Tmax, int len, float scale, const int* pos_dev, int append, cudaStream_t st);
+/* Split-KV form (same contract): grid (H, B, splits), each CTA takes 1/splits of the cached keys with coalesced row
+ * loads (8 key + 8 value rows in flight per warp); the last CTA of a (b, h) pair to arrive merges the partials.
+ * scratch: B*H*splits*(hs+2) floats; tickets: B*H zeroed unsigned ints (left zero); splits == 1 needs neither. */
+int b200_attn_decode_split(const void* qkv, void* kcache, void* vcache, void* out, float* scratch, void* tickets, int B, int H, int hs, int Tmax, int len, float scale, const int* pos_dev, int append, int splits, cudaStream_t st);
 /* next[b] ~ softmax(logits[b, :] / temperature) restricted to the top_k largest (top_k <= 0: all);
  * Philox-free counter RNG: (seed, step, b) -> uniform.  logits bf16 [B, ld]. */
 int b200_sample(const void* logits, long long ld, long long* next, int B, int V, float temperature, int top_k, unsigned long long seed, unsigned long long step, const int* pos_dev, cudaStream_t st);

@@ -302,6 +302,15 @@ def attn_decode(qkv, kcache, vcache, out, B, H, hs, Tmax, length=1, pos_dev=None
                                      1.0 / math.sqrt(hs), _p(pos_dev), int(append), _st()), "attn_decode")
 
 
+def attn_decode_split(qkv, kcache, vcache, out, B, H, hs, Tmax, scratch, tickets, splits: int, length=1, pos_dev=None,
+                      append: bool = False):
+    """Split-KV decode attention: scratch fp32 [B*H*splits*(hs+2)], tickets int32 [B*H] (zeroed once)."""
+    assert splits == 1 or (scratch.numel() >= B * H * splits * (hs + 2) and tickets.numel() >= B * H)
+    _chk(lib.load().b200_attn_decode_split(_p(qkv), _p(kcache), _p(vcache), _p(out), _p(scratch), _p(tickets), B, H, hs, Tmax,
+                                           length, 1.0 / math.sqrt(hs), _p(pos_dev), int(append), splits, _st()),
+         "attn_decode")
+
+
 def sample(logits, next_tok, V, temperature=1.0, seed=0, step=0, pos_dev=None):
     B = logits.shape[0]
     _chk(lib.load().b200_sample(_p(logits), logits.stride(0), _p(next_tok), B, V, float(temperature), 0, seed, step,

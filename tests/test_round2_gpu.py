@@ -322,3 +322,33 @@ def test_embed_bwd_sorted_is_deterministic_and_matches_index_add(ops):
     assert _rel(outs[0][1], dx.view(B, T, d).sum(0)) < 1e-6
     ops.embed_bwd_sorted(idx, order, dx, outs[0][0], outs[0][1], accumulate=True)
     assert _rel(outs[0][0], 2 * ref) < 1e-6
+
+
+@pytest.mark.parametrize("hs", [64, 128])
+@pytest.mark.parametrize("splits", [1, 3, 8])
+@pytest.mark.parametrize("L", [1, 37, 700])
+def test_decode_attention_split_kv(ops, hs, splits, L):
+    """Split-KV decode attention (coalesced rows, partials merged by the last CTA) against the fp32 oracle, with and
+    without the fused KV append, twice in a row on the same scratch / tickets."""
+    torch.manual_seed(L + splits)
+    B, H, Tmax = 3, 4, 1024
+    hist = _rand(B * L, 3 * H * hs)
+    kc = torch.zeros(B, H, Tmax, hs, device="cuda", dtype=BF16)
+    vc = torch.zeros_like(kc)
+    ops.kv_append(hist, kc, vc, B, L, H, hs, Tmax, pos0=0)
+    qkv = hist.view(B, L, -1)[:, -1].contiguous()
+    pos = torch.tensor([L - 1], device="cuda", dtype=torch.int32)
+    scratch = torch.empty(B * H * splits * (hs + 2), device="cuda")
+    tickets = torch.zeros(B * H, device="cuda", dtype=torch.int32)
+    ref = _ref_attn(hist.float(), B, L, H, hs).view(B, L, -1)[:, -1]
+    for rep in range(2):
+        out = torch.empty(B, H * hs, device="cuda", dtype=BF16)
+        ops.attn_decode_split(qkv, kc, vc, out, B, H, hs, Tmax, scratch, tickets, splits, pos_dev=pos)
+        assert _rel(out, ref) < 8e-3, (rep, _rel(out, ref))
+        assert int(tickets.abs().sum()) == 0
+    kc2, vc2 = kc.clone(), vc.clone()
+    kc2[:, :, L - 1] = 0
+    vc2[:, :, L - 1] = 0
+    out2 = torch.empty_like(out)
+    ops.attn_decode_split(qkv, kc2, vc2, out2, B, H, hs, Tmax, scratch, tickets, splits, pos_dev=pos, append=True)
+    assert _rel(out2, ref) < 8e-3 and torch.equal(kc2, kc) and torch.equal(vc2, vc)
