@@ -63,6 +63,9 @@ class VocabParallelHead:
         self.m_b = torch.zeros((self.n_local + 3) // 4 * 4, device=eng.device, dtype=F32)
         self.v_b = torch.zeros_like(self.m_b)
         self.hyper = torch.zeros(8, device=eng.device, dtype=F32)
+        # hand-shake generation: one per forward pass (NOT the optimizer-step epoch - with gradient accumulation several
+        # forward/backward passes share a step, and a flag that already equals the epoch would let a rank run ahead)
+        self.pass_dev = torch.zeros(1, device=eng.device, dtype=torch.int32)
 
     # views of the owned slice
     def _w(self, flat):
@@ -87,7 +90,8 @@ class VocabParallelHead:
         vw = self.workspace(w.M)
         d, V, W, r = eng.layout.d, eng.layout.V, self.world, self.rank
         st = torch.cuda.current_stream().cuda_stream
-        ep, err = self.dp.epoch_dev.data_ptr(), self.dp.err.data_ptr()
+        ops.incr_int(self.pass_dev, 1)
+        ep, err = self.pass_dev.data_ptr(), self.dp.err.data_ptr()
         vw.hf.view(BF16)[:w.M * d].view(w.M, d).copy_(w.hf)
         vw.tgt.view(torch.int64)[:w.M].copy_(w.tgt.view(-1))
         lib.check(L.b200_vp_gather_rows(self._arr(vw.hf), self._arr(vw.tgt), vw.hf_all.data_ptr(), vw.tgt_all.data_ptr(),
@@ -108,7 +112,7 @@ class VocabParallelHead:
         vw = self.workspace(w.M)
         d, W, r = eng.layout.d, self.world, self.rank
         st = torch.cuda.current_stream().cuda_stream
-        ep, err = self.dp.epoch_dev.data_ptr(), self.dp.err.data_ptr()
+        ep, err = self.pass_dev.data_ptr(), self.dp.err.data_ptr()
         lib.check(L.b200_vp_barrier(self._arr(self.sig), W, r, 2, ep, err, st), "vp_barrier")   # lse_all complete
         logits = vw.logits.view(BF16)[:vw.Mw * self.ldl].view(vw.Mw, self.ldl)[:, :self.n_local]
         lse_all = vw.lse_all.view(F32)[:vw.Mw]

@@ -71,7 +71,14 @@ def main():
     # (3) gather full state
     eng.dp.gather_full_state()
     if eng.dp.vp is not None or eng.dp.zero:
-        ref = eng.wb.clone(); dist.broadcast(ref, src=0); same2 = torch.equal(eng.wb, ref)
+        # the gathered fp32 masters (and, outside the owner-kept embedding tables, the bf16 weights) must be bit-identical
+        lo = eng.layout.embed_range[1] if getattr(eng.dp, "shard_embed", False) else 0
+        mine = [eng.flat[:eng.layout.total], eng.wb[lo:]]
+        same2 = True
+        for t in mine:
+            ref = t.clone()
+            dist.broadcast(ref, src=0)
+            same2 = same2 and torch.equal(t, ref)
         flags2 = [None] * W; dist.all_gather_object(flags2, bool(same2)); flags = flags2
     ok = all(flags)
     if r == 0:
