@@ -81,7 +81,11 @@ def run_reference_bench(args, root: str, m: dict, lr: float) -> None:
             print(f"[reference] torch.compile unavailable: {e}", file=sys.stderr)
     if world > 1:
         from torch.nn.parallel import DistributedDataParallel as DDP
-        model = DDP(model, device_ids=[ref.ddp_local_rank])
+        # stock path: DDP(model, device_ids=[...]) exactly as the reference writes it.  REF_BROADCAST_BUFFERS=0 is an
+        # information-only variant: it stops DDP from re-broadcasting the 576 MiB of tril mask buffers
+        # every step; the driver's arm never sets it.
+        ddp_kw = {} if os.environ.get("REF_BROADCAST_BUFFERS", "1") == "1" else {"broadcast_buffers": False}
+        model = DDP(model, device_ids=[ref.ddp_local_rank], **ddp_kw)
     optimizer = torch.optim.AdamW(model.parameters(), lr=config["t_lr"])
     train_it = get_batch_iterator(data_path, B, T, device, world > 1, rank, world)
     trainer = ref.Trainer(model, train_it, train_it, optimizer)
@@ -186,7 +190,9 @@ def run_reference_bench(args, root: str, m: dict, lr: float) -> None:
                        "l2": "no flush: per-step working set (activations + weights + optimizer state, >4 GB) "
                              "is far larger than the 126 MB L2"},
             "arm_details": {"torch_compile": compiled,
-                            "ddp": "torch DDP/NCCL, sync every step" if world > 1 else "none",
+                            "ddp": ("torch DDP/NCCL, sync every step" + ("" if os.environ.get("REF_BROADCAST_BUFFERS", "1") == "1"
+                                                                             else ", broadcast_buffers=False (variant)"))
+                                   if world > 1 else "none",
                             "reference_root": root},
             "final_loss": final_loss, "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": 0,
         }), flush=True)
