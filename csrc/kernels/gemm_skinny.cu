@@ -179,16 +179,29 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             const int rows = (p.M + p.splits - 1) / p.splits;          // batch rows reduced by this CTA
             const int m_lo = split * rows, m_hi = min(p.M, m_lo + rows);
             const uint32_t local = smem_base;                          // same offset in every CTA of the cluster
-            for (int m = m_lo; m < m_hi; ++m) {
-                float v = b;
-                for (int s2 = 0; s2 < p.splits; ++s2) {
-                    float t;
-                    const uint32_t ra = ptx::mapa(local + (uint32_t)(m * 128 + nl) * 4u, (uint32_t)s2);
-                    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(t) : "r"(ra) : "memory");
-                    v += t;
+            // 4 rows x up to 8 peers = 32 independent distributed-shared-memory loads in flight before the first add
+            // (a remote load is ~215 clk away: the dependent one-at-a-time loop this replaces cost 3-4 us per GEMM)
+            for (int m0 = m_lo; m0 < m_hi; m0 += 4) {
+                float t[4][8];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int s2 = 0; s2 < 8; ++s2) {
+                        t[r][s2] = 0.f;
+                        if (s2 < p.splits && m0 + r < m_hi) {
+                            const uint32_t ra = ptx::mapa(local + (uint32_t)((m0 + r) * 128 + nl) * 4u, (uint32_t)s2);
+                            asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(t[r][s2]) : "r"(ra) : "memory");
+                        }
+                    }
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    if (m0 + r >= m_hi) break;
+                    float v = b;
+#pragma unroll
+                    for (int s2 = 0; s2 < 8; ++s2) v += t[r][s2];
+                    if (p.relu) v = fmaxf(v, 0.f);
+                    if (n < p.N) p.out[(size_t)(m0 + r) * p.ldc + n] = __float2bfloat16_rn(v);
                 }
-                if (p.relu) v = fmaxf(v, 0.f);
-                if (n < p.N) p.out[(size_t)m * p.ldc + n] = __float2bfloat16_rn(v);
             }
         }
         ptx::cluster_sync_all();                                       // nobody leaves while its tile may still be read
@@ -251,8 +264,15 @@ extern "C" int b200_gemm_skinny_splits(int M, int N, int K) {
         while (s > 1 && num_kb / s < 4) --s;
         return s;
     }
-    int splits = 1;
-    while (splits < 8 && n_tiles * splits * 2 <= sms + sms / 4 && num_kb / (splits * 2) >= 4) splits *= 2;
+    // Measured on B200 in graph replay (tools/bench_skinny.py, M = 32, 1.3B shapes): one CTA streams ~70 GB/s whatever
+    // the split, a cluster costs ~1 us (co-scheduling, two cluster barriers, the DSMEM reduction), so splitting K only
+    // pays when there are few weight-row tiles: QKV (48 tiles) 7.5 us unsplit vs 8.6 with 2 CTAs per tile, MLP-up (64
+    // tiles) 8.2 vs 9.3, MLP-down (16 tiles) 16.1 unsplit, 9.3 with 4, 13.3 with 8.  Rule: about 72 CTAs in all.
+    int splits = (72 + n_tiles / 2) / n_tiles;
+    splits = splits < 1 ? 1 : (splits > 8 ? 8 : splits);
+    if (splits == 3) splits = 4;                       // odd cluster sizes schedule badly (12.5 us vs 9.8 for QKV)
+    if (splits == 5 || splits == 7) splits -= 1;
+    while (splits > 1 && num_kb / splits < 4) --splits;
     return splits;
 }
 
