@@ -160,13 +160,15 @@ class DataParallel:
         torch.cuda.synchronize()
 
     # ------------------------------------------------------------------ per-step protocol
-    def bucket_ready(self, name: str) -> None:
+    def bucket_ready(self, name: str, also=None) -> None:
         """Called by Engine.backward right after the bucket's last gradient kernel was enqueued."""
         b = self.index[name]
         main = torch.cuda.current_stream()
         ev = torch.cuda.Event()
         ev.record(main)
         self.comm_stream.wait_event(ev)
+        if also is not None:                   # the bucket's weight gradients are produced on their own stream
+            self.comm_stream.wait_event(also)
         self._launch(b)
 
     def _launch(self, b: int, tail: bool = False) -> None:

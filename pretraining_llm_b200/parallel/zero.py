@@ -353,12 +353,14 @@ class ZeroDataParallel:
         lib.check(rc, "zero_wait")
         ops.LAUNCHES += 1
 
-    def bucket_ready(self, name: str) -> None:
+    def bucket_ready(self, name: str, also=None) -> None:
         b = self.index[name]
         main = torch.cuda.current_stream()
         ev = torch.cuda.Event()
         ev.record(main)
         self.comm_stream.wait_event(ev)
+        if also is not None:                   # the bucket's weight gradients are produced on their own stream
+            self.comm_stream.wait_event(also)
         self._launch(b)
 
     def _launch(self, b: int) -> None:
@@ -461,6 +463,9 @@ class ZeroDataParallel:
                 self.v[o:o + cnt].copy_(eng.exp_avg_sq[s:s + cnt])
             eng.release_full_opt_state()
         self.release_full()
+        if self.world > 1:                 # the peers' all-gathers read these shards: nobody runs ahead of the re-shard
+            torch.cuda.synchronize()
+            dist.barrier()
 
     def memory_report(self) -> Dict[str, float]:
         rep = {k: v / 2 ** 30 for k, v in self.plan.bytes_per_rank().items()}

@@ -38,6 +38,7 @@ BF16, F32 = torch.bfloat16, torch.float32
 # B200_DETERMINISTIC=1: the token-embedding gradient is summed in a fixed order (sort by token) instead of with vector
 # fp32 atomics whose arrival order varies from run to run
 DETERMINISTIC = os.environ.get("B200_DETERMINISTIC", "0") == "1"
+WGRAD_STREAM = os.environ.get("B200_WGRAD_STREAM", "1") == "1"
 
 
 class Workspace:
@@ -74,9 +75,13 @@ class Workspace:
         self.tgt = torch.zeros(B, T, device=dev, dtype=torch.int64)
         if train:
             self.dx = e(M, d, dt=F32)
-            self.dx_bf16 = e(M, d)
-            self.dh = e(M, 4 * d)
-            self.dqkv = e(M, 3 * d)
+            # gradients read by BOTH a dgrad GEMM (main stream) and a wgrad GEMM (weight-gradient stream) are double
+            # buffered by layer parity, so the next layer can overwrite one copy while the other is still being read
+            self.dxa = [e(M, d), e(M, d), e(M, d)]      # bf16 gradient at a block's output (input of its MLP backward);
+                                                        # three: layer l writes layer l-1's copy while layer l+1's wgrad may still read its own
+            self.dxb = e(M, d)                          # bf16 gradient after the MLP branch (attention's dout)
+            self.dh = [e(M, 4 * d), e(M, 4 * d)]
+            self.dqkv = [e(M, 3 * d), e(M, 3 * d)]
             self.dtmp = e(M, d)
             self.delta = e(B, H, T, dt=F32)
             self.dq_acc = torch.zeros(M, d, device=dev, dtype=F32) if ops.ATTN_BWD_IMPL != "tc" else None
@@ -106,6 +111,9 @@ class Engine:
         self.hyper = torch.zeros(8, device=self.device, dtype=F32)
         self.betas, self.eps, self.weight_decay = (0.9, 0.999), 1e-8, 0.01   # torch.optim.AdamW defaults
         self.ws: Dict[Tuple[int, int, bool], Workspace] = {}
+        # weight gradients run on their own stream: nothing in the backward chain waits for them, so their CTAs fill the
+        # SMs the dgrad GEMMs' last partial wave leaves idle and overlap the memory-bound LayerNorm / attention kernels
+        self.wstream = torch.cuda.Stream(device=self.device) if WGRAD_STREAM else None
         self.dp = None                     # parallel.dp.DataParallel / parallel.zero.ZeroDataParallel
         self.store = None                  # sharded mode: the object that serves P / W / G instead of the flat buffers
         self.launches_per_step = 0
@@ -254,48 +262,86 @@ class Engine:
             z.begin_pass()
         if not accumulate:
             ops.zero_(self.G("token_embed.weight"))  # scatter-add target (memset node, not a fill kernel)
+        main = torch.cuda.current_stream()
+        ws = self.wstream
+        pending = []                                 # one event per layer: its weight gradients are complete
+        used_w = [False]                             # an event of a stream that never joined a capture must not be waited on
+
+        def on_w(fn):
+            """Run fn on the weight-gradient stream after everything enqueued on the main stream so far."""
+            if ws is None:
+                fn()
+                return
+            ev = torch.cuda.Event()
+            ev.record(main)
+            ws.wait_event(ev)
+            used_w[0] = True
+            with torch.cuda.stream(ws):
+                fn()
+
+        def w_done():
+            if ws is None or not used_w[0]:
+                return None
+            ev = torch.cuda.Event()
+            ev.record(ws)
+            return ev
+
         # LM head + CE
         if self.dp is not None and self.dp.vp is not None:
             self.dp.vp.backward(w, grad_scale, accumulate)
         else:
             dlog = w.logits[:, :V]
             ops.ce_grad(dlog, w.ce_lse, w.tgt.view(-1), self.G("lm_head.bias"), V, grad_scale / M, accumulate=accumulate)
-            ops.gemm(dlog, w.hf, out=self.G("lm_head.weight"), a_mn=True, b_mn=True, f32_mode=fm)
+            on_w(lambda: ops.gemm(dlog, w.hf, out=self.G("lm_head.weight"), a_mn=True, b_mn=True, f32_mode=fm))
             ops.gemm(dlog, self.W("lm_head.weight"), out=w.dtmp, b_mn=True)
         stf = w.ln_stats[2 * L]
         ops.ln_bwd(w.dtmp, w.resid_a[L], stf[0], stf[1], self.P("layer_norm.weight"), self.G("layer_norm.weight"),
-                   self.G("layer_norm.bias"), dx_out=w.dx, dx_bf16=w.dx_bf16, partial=w.ln_partial, accumulate=accumulate)
+                   self.G("layer_norm.bias"), dx_out=w.dx, dx_bf16=w.dxa[(L - 1) % 3], partial=w.ln_partial,
+                   accumulate=accumulate)
+        head_done = w_done()
         if dp is not None:
-            dp.bucket_ready("head")
+            dp.bucket_ready("head", head_done)
         for l in reversed(range(L)):
             pre = f"attn_blocks.{l}."
             st1, st2 = w.ln_stats[2 * l], w.ln_stats[2 * l + 1]
+            par = l & 1
+            dxa, dh, dqkv = w.dxa[l % 3], w.dh[par], w.dqkv[par]
+            if ws is not None and len(pending) >= 2:
+                main.wait_event(pending[-2])   # layer l+2's weight gradients have finished reading this parity's buffers
             if z is not None:
                 z.before_layer_bwd(l)          # the gradient window of layer l+2 must have been reduced by every rank
             # ---- MLP
-            ops.gemm(w.dx_bf16, w.act[l], out=self.G(pre + "mlp.proj.weight"), a_mn=True, b_mn=True, f32_mode=fm)
-            ops.gemm(w.dx_bf16, self.W(pre + "mlp.proj.weight"), out=w.dh, b_mn=True, relu_bits=w.relu_bits[l])
-            ops.colsum(w.dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
-            ops.gemm(w.dh, w.h2[l], out=self.G(pre + "mlp.hidden.weight"), a_mn=True, b_mn=True, f32_mode=fm)
+            on_w(lambda: ops.gemm(dxa, w.act[l], out=self.G(pre + "mlp.proj.weight"), a_mn=True, b_mn=True, f32_mode=fm))
+            ops.gemm(dxa, self.W(pre + "mlp.proj.weight"), out=dh, b_mn=True, relu_bits=w.relu_bits[l])
+
+            def mlp_up_wgrad():
+                ops.colsum(dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
+                ops.gemm(dh, w.h2[l], out=self.G(pre + "mlp.hidden.weight"), a_mn=True, b_mn=True, f32_mode=fm)
+            on_w(mlp_up_wgrad)
             if z is not None:                  # carries the all-gather of layer l-1's weights for its backward
-                z.gemm_bwd(l, w.dh, w.dtmp)
+                z.gemm_bwd(l, dh, w.dtmp)
             else:
-                ops.gemm(w.dh, self.W(pre + "mlp.hidden.weight"), out=w.dtmp, b_mn=True)
+                ops.gemm(dh, self.W(pre + "mlp.hidden.weight"), out=w.dtmp, b_mn=True)
             # LayerNorm backward in two steps: the partial sums of ln2 and ln1 are reduced by ONE launch at the end of the block
             ops.ln_bwd_partial(w.dtmp, w.resid_b[l], st2[0], st2[1], self.P(pre + "ln2.weight"), w.ln_partial,
-                               dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16, with_colsum=True)
+                               dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dxb, with_colsum=True)
             # ---- attention
-            ops.attn_bwd(w.qkv[l], w.att[l], w.dx_bf16, w.lse[l], B, T, H, hs, dqkv=w.dqkv, delta=w.delta,
+            ops.attn_bwd(w.qkv[l], w.att[l], w.dxb, w.lse[l], B, T, H, hs, dqkv=dqkv, delta=w.delta,
                          dq_acc=w.dq_acc)
-            ops.gemm(w.dqkv, w.h1[l], out=self.G(pre + "attn.wqkv"), a_mn=True, b_mn=True, f32_mode=fm)
-            ops.gemm(w.dqkv, self.W(pre + "attn.wqkv"), out=w.dtmp, b_mn=True)
+            on_w(lambda: ops.gemm(dqkv, w.h1[l], out=self.G(pre + "attn.wqkv"), a_mn=True, b_mn=True, f32_mode=fm))
+            ops.gemm(dqkv, self.W(pre + "attn.wqkv"), out=w.dtmp, b_mn=True)
             ops.ln_bwd_partial(w.dtmp, w.resid_a[l], st1[0], st1[1], self.P(pre + "ln1.weight"), w.ln_partial2,
-                               dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dx_bf16)
+                               dx_in=w.dx, dx_out=w.dx, dx_bf16=w.dxa[(l - 1) % 3])
             ops.ln_bwd_finalize2(w.M, lay.d, w.ln_partial, self.G(pre + "ln2.weight"), self.G(pre + "ln2.bias"),
                                  self.G(pre + "mlp.proj.bias"), w.ln_partial2, self.G(pre + "ln1.weight"),
                                  self.G(pre + "ln1.bias"), None, accumulate=accumulate)
+            done = w_done()
+            if done is not None:
+                pending.append(done)
             if dp is not None:
-                dp.bucket_ready(f"block{l}")
+                dp.bucket_ready(f"block{l}", done)
+        for ev in pending[-2:] + ([head_done] if head_done is not None else []):
+            main.wait_event(ev)                # join: the optimizer (and the end of a graph capture) follow on the main stream
         if DETERMINISTIC:
             # stable sort of the token ids (torch.sort, capturable) -> runs of equal tokens summed in position order
             order = torch.sort(w.idx.view(-1), stable=True).indices

@@ -213,6 +213,11 @@ class Trainer:
                                                "exp_avg_sq": lay.view(v, name).clone().to(p.device)}
         if sharded and self.model.engine.dp.full_flat is not None:
             self.model.engine.dp.state_loaded()    # no optimizer state in the file: re-shard the weights alone
+        if self.native and self.dist.world > 1:
+            # peers read each other's memory (weight shards, embedding rows): nobody starts a step before every rank
+            # has finished loading
+            torch.cuda.synchronize()
+            self.dist.barrier()
         ts = ckpt.get("trainer_state")
         if ts:
             self.step = int(ts["step"])
