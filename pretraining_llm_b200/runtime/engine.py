@@ -210,6 +210,8 @@ class Engine:
         B, T = idx.shape
         if T > self.layout.ctx:
             raise IndexError(f"sequence length {T} exceeds context_length {self.layout.ctx}")
+        if train and self.dp is not None and getattr(self.dp, "full_flat", None) is not None:
+            self.dp.release_full()
         w = self.workspace(B, T, train)
         self.sync_weights()
         if idx.data_ptr() != w.idx.data_ptr():
@@ -392,6 +394,8 @@ class Engine:
         tensor (no host sync).  From the second call with the same shape the step is one CUDA
         graph replay."""
         B, T = idx.shape
+        if self.dp is not None and getattr(self.dp, "full_flat", None) is not None:
+            self.dp.release_full()         # sharded mode was materialised (generation / checkpoint): back to the shards
         w = self.workspace(B, T, True)
         self.ensure_grad()
         if self.dp is None:
