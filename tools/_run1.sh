@@ -1,6 +1,4 @@
-python -m pytest tests/test_model_gpu.py tests/test_round2_gpu.py -m gpu -x -q 2>&1 | tail -3
-python bench.py --steps 20 --warmup 5 --skip-e2e > gpurun_out/r2_b1_ws.json 2> gpurun_out/r2_b1_ws.err; echo "wstream $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_b1_ws.json | head -1)"; tail -2 gpurun_out/r2_b1_ws.err
-B200_WGRAD_STREAM=0 python bench.py --steps 20 --warmup 5 --skip-e2e > gpurun_out/r2_b1_nows.json 2> gpurun_out/r2_b1_nows.err; echo "single stream $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_b1_nows.json | head -1)"
-python bench.py --steps 20 --warmup 5 --skip-e2e > gpurun_out/r2_b1_ws2.json 2>/dev/null; echo "wstream again $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_b1_ws2.json | head -1)"
-python bench.py --steps 10 --warmup 3 --skip-e2e --model 1.3b > gpurun_out/r2_b1_ws_1p3b.json 2>/dev/null; echo "1.3b wstream $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_b1_ws_1p3b.json | head -1)"
-B200_WGRAD_STREAM=0 python bench.py --steps 10 --warmup 3 --skip-e2e --model 1.3b > gpurun_out/r2_b1_nows_1p3b.json 2>/dev/null; echo "1.3b single $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_b1_nows_1p3b.json | head -1)"
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
+python bench.py > gpurun_out/r2_final_b1.json 2> gpurun_out/r2_final_b1.err; echo "bench rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_final_b1.json | head -1) $(grep -o '"value": [0-9.]*' gpurun_out/r2_final_b1.json | head -1)"
+python bench.py --impl reference > gpurun_out/r2_final_b1_ref.json 2> gpurun_out/r2_final_b1_ref.err; echo "ref rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_final_b1_ref.json | head -1) $(grep -o '"value": [0-9.]*' gpurun_out/r2_final_b1_ref.json | head -1)"
