@@ -21,9 +21,17 @@ from src.models.transformer import Transformer  # noqa: E402
 
 def _load_model(model_path: str, device: str) -> Transformer:
     checkpoint = torch.load(model_path, map_location="cpu", weights_only=False)
-    model = Transformer(n_head=config["n_head"], n_embed=config["n_embed"],
-                        context_length=config["context_length"], vocab_size=config["vocab_size"],
-                        N_BLOCKS=config["n_blocks"])
+    # The reference builds the model from config/config.py (generate_text.py:12-20), so a checkpoint of another shape
+    # needs the config edited first.  Checkpoints written by this framework's Trainer also carry the shape they were
+    # trained with ("trainer_state" -> "config"): prefer it, fall back to the config file for reference checkpoints.
+    shape = dict(config)
+    saved = (checkpoint.get("trainer_state") or {}).get("config") or {}
+    for k in ("n_head", "n_embed", "context_length", "vocab_size", "n_blocks"):
+        if k in saved:
+            shape[k] = saved[k]
+    model = Transformer(n_head=shape["n_head"], n_embed=shape["n_embed"],
+                        context_length=shape["context_length"], vocab_size=shape["vocab_size"],
+                        N_BLOCKS=shape["n_blocks"])
     model.load_state_dict(checkpoint["model_state_dict"])
     return model.eval().to(device)
 
