@@ -44,14 +44,22 @@ void b200_set_error(const char* fmt, ...);
 // Launch helper.  Programmatic dependent launch is OPT-IN (B200_PDL=1): measured on B200 it is neutral for the
 // training step (818.7k vs 823.9k tokens/s, within noise) and slower for the decode step (11.6k vs 15.4k
 // tokens/s at batch 32: early-resident dependents of the many tiny kernels get in the way), so it stays off.
-template <typename... KArgs, typename... Args>
+// B200_PDL: 0 / unset = off, 1 = every kernel, 2 = only the kernels that ask for it (the CTA-pair GEMM, whose prologue -
+// tensor-map prefetch, barrier init, TMEM allocation - is long enough to be worth overlapping with the previous kernel's tail)
+static inline int b200_pdl_mode() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("B200_PDL");
+        mode = (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 0;
+    }
+    return mode;
+}
+
+template <bool WANTS_PDL = false, typename... KArgs, typename... Args>
 static inline cudaError_t b200_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                                       Args&&... args) {
-    static int pdl = -1;
-    if (pdl < 0) {
-        const char* e = getenv("B200_PDL");
-        pdl = (e != nullptr && e[0] == '1') ? 1 : 0;
-    }
+    const int mode = b200_pdl_mode();
+    const int pdl = (mode == 1 || (mode == 2 && WANTS_PDL)) ? 1 : 0;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = grid;

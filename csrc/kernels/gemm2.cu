@@ -283,7 +283,7 @@ int launch2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC,
     }
     AgParams none;
     memset(&none, 0, sizeof(none));
-    B200_CHECK_CUDA(b200_launch(kern, dim3(grid), dim3(NUM_THREADS + 128), Cfg2<BN>::SMEM_BYTES, st, tA, tB, tC, p, ag ? *ag : none));
+    B200_CHECK_CUDA(b200_launch<true>(kern, dim3(grid), dim3(NUM_THREADS + 128), Cfg2<BN>::SMEM_BYTES, st, tA, tB, tC, p, ag ? *ag : none));
     return 0;
 }
 
