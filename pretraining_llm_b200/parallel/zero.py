@@ -162,7 +162,8 @@ class ZeroDataParallel:
         self.small = self.sym_small.view(F32)[:plan.small_elems]
         self.sym_sig = sb(2 * W * self.nb * 4)
         mcs = [b.mc_ptr for b in (*self.sym_gwin, self.sym_head_g, self.sym_embed_g, self.sym_small)]
-        self.multicast = all(mcs) and os.environ.get("B200_DP_MULTIMEM", "1") == "1"
+        want = os.environ.get("B200_DP_MULTIMEM", "auto")      # same policy as the replicated mode: on from 4 ranks
+        self.multicast = all(mcs) and (want == "1" or (want == "auto" and W >= 4))
         # ---- device-side protocol state
         z = lambda *s: torch.zeros(*s, device=dev, dtype=torch.int32)
         self.flags, self.counters = z(self.nb, W), z(self.nb, W)
