@@ -86,6 +86,9 @@ class Transformer(nn.Module):
         from ..ops import lib
         return lib.available()
 
+    def _engine_has_full_params(self) -> bool:
+        return self._flat is not None and (self._engine is None or getattr(self._engine, "store", None) is None)
+
     @property
     def engine(self):
         if self._engine is None:
@@ -126,7 +129,10 @@ class Transformer(nn.Module):
 
         Equals the reference (transformer.py:80-94) for N_BLOCKS == 1.  For deeper models the
         reference feeds a (B,T,4d) tensor into the next block and raises; here
-        blocks 0..L-2 run normally and the last block reports its embedding."""
+        blocks 0..L-2 run normally and the last block reports its embedding.  On a CUDA model the sweep runs on the
+        native kernels (bf16 compute, fp32 copies returned) unless gradients are wanted."""
+        if self._native_ok() and not torch.is_grad_enabled() and self._engine_has_full_params():
+            return self.engine.forward_embedding(idx)
         x = self._pre_attn_pass(idx)
         residual = x
         for i, block in enumerate(self.attn_blocks):

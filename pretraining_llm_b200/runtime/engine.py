@@ -35,8 +35,9 @@ from .. import ops
 from ..utils import nvtx
 
 BF16, F32 = torch.bfloat16, torch.float32
-# B200_DETERMINISTIC=1: the token-embedding gradient is summed in a fixed order (sort by token) instead of with vector
-# fp32 atomics whose arrival order varies from run to run
+# B200_DETERMINISTIC=1: every gradient is summed in a fixed order - the token-embedding gradient by sorting the tokens,
+# the bias gradients by one CTA per column strip - instead of with fp32 atomics whose arrival order varies from run to
+# run (the other kernels - GEMMs without split-K, attention, LayerNorm - are order-deterministic already)
 DETERMINISTIC = os.environ.get("B200_DETERMINISTIC", "0") == "1"
 WGRAD_STREAM = os.environ.get("B200_WGRAD_STREAM", "1") == "1"
 
@@ -293,7 +294,12 @@ class Engine:
             self.dp.vp.backward(w, grad_scale, accumulate)
         else:
             dlog = w.logits[:, :V]
-            ops.ce_grad(dlog, w.ce_lse, w.tgt.view(-1), self.G("lm_head.bias"), V, grad_scale / M, accumulate=accumulate)
+            if DETERMINISTIC:      # bias gradient by the fixed-order column-sum kernel instead of per-CTA fp32 atomics
+                ops.ce_grad(dlog, w.ce_lse, w.tgt.view(-1), None, V, grad_scale / M, accumulate=accumulate)
+                ops.colsum(dlog, out=self.G("lm_head.bias"), accumulate=accumulate)
+            else:
+                ops.ce_grad(dlog, w.ce_lse, w.tgt.view(-1), self.G("lm_head.bias"), V, grad_scale / M,
+                            accumulate=accumulate)
             on_w(lambda: ops.gemm(dlog, w.hf, out=self.G("lm_head.weight"), a_mn=True, b_mn=True, f32_mode=fm))
             ops.gemm(dlog, self.W("lm_head.weight"), out=w.dtmp, b_mn=True)
         stf = w.ln_stats[2 * L]
@@ -445,6 +451,25 @@ class Engine:
         params = [p for _, p in self.model.named_parameters()]
         loss, logits = _EngineLoss.apply(self, idx, targets, *params)
         return logits, loss
+
+    def forward_embedding(self, idx: torch.Tensor):
+        """(post-ReLU hidden of the last block (B,T,4d), its residual input (B,T,d)) on the native kernels - the
+        reference's ``Transformer.forward_embedding`` (src/models/transformer.py:80-94), fp32 copies of the bf16 / fp32
+        workspace tensors (the inference workspace reuses one slot per layer, so after the sweep it holds the LAST
+        block's activations)."""
+        if self.store is not None:
+            raise RuntimeError("forward_embedding needs full parameters; with dp_mode='zero' call engine.dp.materialize() first")
+        idx = idx.contiguous().long()
+        B, T = idx.shape
+        if T > self.layout.ctx:
+            raise IndexError(f"sequence length {T} exceeds context_length {self.layout.ctx}")
+        w = self.workspace(B, T, False)
+        self.sync_weights()
+        w.idx.copy_(idx)
+        ops.embed_fwd(w.idx, self.P("token_embed.weight"), self.P("position_embed.weight"), out=w.resid_a[0])
+        self._blocks_forward(w)
+        d = self.layout.d
+        return w.act[0].view(B, T, 4 * d).float(), w.resid_b[0].view(B, T, d).clone()
 
     # ------------------------------------------------------------------ generation
     def generate(self, idx, max_new_tokens, **kw):

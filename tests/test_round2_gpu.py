@@ -352,3 +352,49 @@ def test_decode_attention_split_kv(ops, hs, splits, L):
     out2 = torch.empty_like(out)
     ops.attn_decode_split(qkv, kc2, vc2, out2, B, H, hs, Tmax, scratch, tickets, splits, pos_dev=pos, append=True)
     assert _rel(out2, ref) < 8e-3 and torch.equal(kc2, kc) and torch.equal(vc2, vc)
+
+
+def test_deterministic_mode_gives_bit_identical_gradients():
+    """B200_DETERMINISTIC=1 (read at import / first launch, hence the subprocess): two backward passes from the same
+    weights on the same batch produce bit-identical gradient buffers - embedding scatter, bias column sums included."""
+    import subprocess
+    code = (
+        "import torch, sys; sys.path.insert(0, %r)\n"
+        "from pretraining_llm_b200.models import Transformer\n"
+        "torch.manual_seed(0)\n"
+        "m = Transformer(n_head=4, n_embed=256, context_length=256, vocab_size=5000, N_BLOCKS=3).cuda()\n"
+        "e = m.engine\n"
+        "x = (torch.rand(8, 256, device='cuda') ** 3 * 5000).long(); y = torch.randint(0, 5000, (8, 256), device='cuda')\n"
+        "gs = []\n"
+        "for _ in range(3):\n"
+        "    w, _, loss = e.forward(x, y, train=True); e.backward(w); torch.cuda.synchronize(); gs.append(e.grad.clone())\n"
+        "assert torch.equal(gs[0], gs[1]) and torch.equal(gs[1], gs[2]), 'gradients differ between runs'\n"
+        "assert float(gs[0].abs().sum()) > 0\n"
+        "print('DETERMINISTIC_OK')\n") % ROOT
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, B200_DETERMINISTIC="1"))
+    assert r.returncode == 0 and "DETERMINISTIC_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_forward_embedding_runs_on_the_native_kernels():
+    """Transformer.forward_embedding on a CUDA model (no grad) takes the engine's kernels and matches the PyTorch
+    statement of the same blocks; with gradients enabled it stays on the differentiable PyTorch path."""
+    from pretraining_llm_b200 import ops as _ops
+    from pretraining_llm_b200.models import Transformer
+    torch.manual_seed(6)
+    cfg = dict(n_head=4, n_embed=256, context_length=128, vocab_size=1000)
+    m = Transformer(**cfg, N_BLOCKS=3).cuda()
+    o = Transformer(**cfg, N_BLOCKS=3).cuda()
+    o.load_state_dict(m.state_dict())
+    o.use_native = False
+    x = torch.randint(0, 1000, (2, 100), device="cuda")
+    n0 = _ops.LAUNCHES
+    with torch.no_grad():
+        hid, res = m.forward_embedding(x)
+        hid_o, res_o = o.forward_embedding(x)
+    assert _ops.LAUNCHES > n0                                   # the native path really ran
+    assert hid.shape == hid_o.shape == (2, 100, 1024) and res.shape == res_o.shape == (2, 100, 256)
+    assert _rel(res, res_o) < 2e-2 and _rel(hid, hid_o) < 3e-2
+    n1 = _ops.LAUNCHES
+    hid_g, _ = m.forward_embedding(x)                           # grad mode: PyTorch path, differentiable
+    assert _ops.LAUNCHES == n1 and hid_g.requires_grad

@@ -1,1 +1,1 @@
-for m in 0 2 0 2; do B200_PDL=$m python bench.py --steps 30 --warmup 5 --skip-e2e > gpurun_out/r2_pdl$m.json 2>/dev/null; echo "B200_PDL=$m $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2_pdl$m.json | head -1)"; done
+python -m pytest tests/test_round2_gpu.py tests/test_model_gpu.py tests/test_kernels_gpu.py -m gpu -x -q 2>&1 | tail -3
