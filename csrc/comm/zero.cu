@@ -40,7 +40,8 @@ __global__ void __launch_bounds__(512) zero_reduce_adamw_kernel(ZrPeers P, int r
                                                                 float* __restrict__ master, float* __restrict__ m,
                                                                 float* __restrict__ v, bf16* __restrict__ shard16,
                                                                 const float* __restrict__ hyper, ZrSlots slots,
-                                                                unsigned int* cta_counter, int* err) {
+                                                                unsigned int* cta_counter, int* err,
+                                                                float* __restrict__ gacc, int accumulate_only) {
     pdl_sync();
     const int epoch = *epoch_dev;
     __shared__ int s_peers_ok;
@@ -87,7 +88,15 @@ __global__ void __launch_bounds__(512) zero_reduce_adamw_kernel(ZrPeers P, int r
             const long long i = base + u * stride;
             if (i >= n4) break;
             const long long e = lo + i * 4;
-            const float4 s = sum[u];
+            float4 s = sum[u];
+            if (gacc != nullptr) {
+                // gradient accumulation over micro-steps: the reduced slice of every micro-step but the last is added to
+                // a 1/W-sized fp32 accumulator (no update); the last one picks the accumulator up and clears it
+                float4 ga = reinterpret_cast<float4*>(gacc)[i];
+                s.x += ga.x; s.y += ga.y; s.z += ga.z; s.w += ga.w;
+                reinterpret_cast<float4*>(gacc)[i] = accumulate_only ? s : make_float4(0.f, 0.f, 0.f, 0.f);
+                if (accumulate_only) continue;
+            }
             float4 pv = reinterpret_cast<float4*>(master)[i];
             float4 mv = reinterpret_cast<float4*>(m)[i];
             float4 vv = reinterpret_cast<float4*>(v)[i];
@@ -174,7 +183,7 @@ extern "C" int b200_zero_reduce_adamw(void* const* h_grad, void* mc_grad, void* 
                                       const int* epoch_dev, long long lo, long long n, float* master, float* m, float* v,
                                       void* shard16, const float* hyper, const long long* h_slot_end,
                                       const long long* h_slot_small_off, int n_slots, void* cta_counter, int* err, int ctas,
-                                      cudaStream_t st) {
+                                      float* gacc, int accumulate_only, cudaStream_t st) {
     B200_REQUIRE(world >= 1 && world <= DP_MAX_WORLD, "zero: world size %d not supported (max %d)", world, DP_MAX_WORLD);
     B200_REQUIRE(n_slots <= ZR_MAX_SLOTS, "zero: too many slots in one bucket");
     B200_REQUIRE(n % 4 == 0 && lo % 4 == 0, "zero: slice must be 16-byte aligned");
@@ -193,10 +202,10 @@ extern "C" int b200_zero_reduce_adamw(void* const* h_grad, void* mc_grad, void* 
 #define ZR_LAUNCH(W_)                                                                                               \
     if (mc)                                                                                                         \
         B200_CHECK_CUDA(b200_launch(zero_reduce_adamw_kernel<W_, true, 4>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, \
-                                    epoch_dev, lo, n, master, m, v, (bf16*)shard16, hyper, S, (unsigned int*)cta_counter, err)); \
+                                    epoch_dev, lo, n, master, m, v, (bf16*)shard16, hyper, S, (unsigned int*)cta_counter, err, gacc, accumulate_only)); \
     else                                                                                                            \
         B200_CHECK_CUDA(b200_launch(zero_reduce_adamw_kernel<W_, false, 1>, dim3(ctas), dim3(512), 0, st, P, rank, bucket, num_buckets, \
-                                    epoch_dev, lo, n, master, m, v, (bf16*)shard16, hyper, S, (unsigned int*)cta_counter, err))
+                                    epoch_dev, lo, n, master, m, v, (bf16*)shard16, hyper, S, (unsigned int*)cta_counter, err, gacc, accumulate_only))
     switch (world) {
         case 1: ZR_LAUNCH(1); break;
         case 2: ZR_LAUNCH(2); break;

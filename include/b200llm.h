@@ -197,8 +197,10 @@ int b200_dp_reduce_adamw(void* const* h_grad, void* const* h_wb, void* const* h_
  * null), the owned slice [lo, lo+n) of the bucket is reduced (multimem.ld_reduce or W peer loads), master / m / v /
  * shard16 are this rank's slices (fp32 master, moments, bf16 shard the peers' all-gather reads), and parameters
  * consumed in fp32 are also stored into every rank's small replicated store (h_small / mc_small) at
- * bucket offset + h_slot_small_off[k] (slots whose value is -(1<<62) are not small). */
-int b200_zero_reduce_adamw(void* const* h_grad, void* mc_grad, void* const* h_small, void* mc_small, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long lo, long long n, float* master, float* m, float* v, void* shard16, const float* hyper, const long long* h_slot_end, const long long* h_slot_small_off, int n_slots, void* cta_counter, int* err, int ctas, cudaStream_t st);
+ * bucket offset + h_slot_small_off[k] (slots whose value is -(1<<62) are not small).  gacc (nullable): this rank's
+ * fp32 accumulator for the slice (gradient accumulation): accumulate_only != 0 adds the reduced slice to it and updates
+ * nothing; otherwise the accumulator is added to the reduced slice, cleared, and the update runs. */
+int b200_zero_reduce_adamw(void* const* h_grad, void* mc_grad, void* const* h_small, void* mc_small, void* const* h_sig, int world, int rank, int bucket, int num_buckets, const int* epoch_dev, long long lo, long long n, float* master, float* m, float* v, void* shard16, const float* hyper, const long long* h_slot_end, const long long* h_slot_small_off, int n_slots, void* cta_counter, int* err, int ctas, float* gacc, int accumulate_only, cudaStream_t st);
 /* blocks the stream until every rank's done flag of buckets [bucket_lo, bucket_hi) has reached *epoch_dev - lag */
 int b200_zero_wait(const int* sig, int world, int num_buckets, int bucket_lo, int bucket_hi, const int* epoch_dev, int lag, int* err, cudaStream_t st);
 /* x[b*T+t, :] = wte[idx[b,t], :] + wpe[t, :] with the fp32 tables sharded: h_shard[r] = rank r's master slice of the

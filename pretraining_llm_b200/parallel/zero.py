@@ -180,6 +180,8 @@ class ZeroDataParallel:
         self._emb_array = self._peer_array(self.sym_master, plan.soff[eb] * 4)
         self._small_array = self.sym_small.ptr_array
         self.full_flat: Optional[torch.Tensor] = None     # only while materialised (checkpoint, generation)
+        self.gacc: Optional[torch.Tensor] = None          # fp32 accumulator over micro-steps (1/W of the model), on demand
+        self._accum_only = False
         # ---- take over the parameters: identical replicas from rank 0, then keep only the owned slices
         if W > 1:
             dist.broadcast(eng.flat, src=0)
@@ -271,6 +273,18 @@ class ZeroDataParallel:
     def begin_step(self) -> None:
         ops.incr_int(self.epoch_dev, 1)
         self._launched = set()
+
+    def begin_backward(self, accumulate: bool, dp_sync: bool) -> None:
+        """Gradient accumulation: the rolling windows cannot hold a running sum, so every micro-step is reduce-scattered
+        as usual and the owner adds its slice to a 1/W-sized fp32 accumulator; the last micro-step (dp_sync) picks the
+        accumulator up and runs AdamW.  Each micro-step is its own hand-shake epoch."""
+        if accumulate:
+            ops.incr_int(self.epoch_dev, 1)
+            self._launched = set()
+        self._accum_only = not dp_sync
+        if (accumulate or not dp_sync) and self.gacc is None:
+            self.gacc = torch.zeros(self.plan.shard_elems, device=self.eng.device, dtype=F32)
+        self.begin_pass()
 
     def begin_pass(self) -> None:
         """Start of a forward or a backward pass: a new gather generation."""
@@ -376,7 +390,8 @@ class ZeroDataParallel:
             ctypes.c_void_p(self.sym_small.mc_ptr) if mc else None, self.sym_sig.ptr_array, self.world, self.rank, b,
             self.nb, self.epoch_dev.data_ptr(), lo, cnt, self.master[o:].data_ptr(), self.m[o:].data_ptr(),
             self.v[o:].data_ptr(), self.shard16[o:].data_ptr(), self.eng.hyper.data_ptr(), ends, smalls, k,
-            self.cta_counter[b:].data_ptr(), self.err.data_ptr(), self.ctas, self.comm_stream.cuda_stream)
+            self.cta_counter[b:].data_ptr(), self.err.data_ptr(), self.ctas,
+            None if self.gacc is None else self.gacc[o:].data_ptr(), int(self._accum_only), self.comm_stream.cuda_stream)
         lib.check(rc, "zero_reduce_adamw")
         ops.LAUNCHES += 1
         self._launched.add(b)

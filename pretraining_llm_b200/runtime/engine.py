@@ -259,10 +259,12 @@ class Engine:
         fm = 1 if accumulate else 0
         z = self.store
         if z is not None:
-            if accumulate or not dp_sync:
-                raise NotImplementedError("sharded mode reduces every layer's gradients as soon as they exist: "
-                                          "gradient accumulation needs dp_mode='ddp'")
-            z.begin_pass()
+            # sharded mode: the gradient windows hold ONE micro-step; each micro-step is reduce-scattered and the owners
+            # accumulate their slices (ZeroDataParallel.begin_backward), so locally nothing is ever accumulated
+            z.begin_backward(accumulate, dp_sync)
+            dp = self.dp
+            fm = 0
+            accumulate = False
         if not accumulate:
             ops.zero_(self.G("token_embed.weight"))  # scatter-add target (memset node, not a fill kernel)
         main = torch.cuda.current_stream()
@@ -360,6 +362,9 @@ class Engine:
                           accumulate=accumulate)
         if not accumulate and T < lay.ctx:
             ops.zero_(self.G("position_embed.weight")[T:])
+        if z is not None and not dp_sync:
+            z.reduce_and_step()                # micro-step of an accumulation: flush the remaining buckets into the
+                                               # accumulators before the next micro-step overwrites the windows
 
     # ------------------------------------------------------------------ optimizer
     def set_hyper(self, lr: float, grad_scale: float = 1.0) -> None:

@@ -191,6 +191,8 @@ def test_zero_mode_single_rank_matches_plain_engine():
     import zero_check1
     zero_check1.run(dict(n_head=4, n_embed=256, context_length=128, vocab_size=1000), 3, 4, 128, 5, 1e-3, False)
     zero_check1.run(dict(n_head=2, n_embed=256, context_length=256, vocab_size=1000), 4, 2, 256, 5, 1e-3, True)
+    # gradient accumulation: every micro-step reduce-scattered into the owners' accumulators, AdamW on the last
+    zero_check1.run_accum(dict(n_head=4, n_embed=256, context_length=128, vocab_size=1000), 3, 4, 128, 3, 1e-3, 3)
 
 
 def test_zero_plan_memory_claim():

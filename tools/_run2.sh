@@ -1,4 +1,2 @@
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1"
-DP_MODE=zero timeout 300 $TR --master-port 29911 tools/dp_check.py > gpurun_out/r2_fin_dpz.log 2>&1; echo "dp_check zero (per-peer) rc=$?"; grep -h "world\|mean|dW|\|DP_CHECK\|Error" gpurun_out/r2_fin_dpz.log | head -4
-DP_MODE=zero DP_SHAPE=small timeout 300 $TR --master-port 29912 tools/dp_check.py > gpurun_out/r2_fin_dpz_small.log 2>&1; echo "dp_check zero d=768 rc=$?"; grep -h "world\|mean|dW|\|DP_CHECK\|Error" gpurun_out/r2_fin_dpz_small.log | head -4
-B200_DP_MULTIMEM=1 DP_MODE=ddp DP_SHAPE=small timeout 300 $TR --master-port 29913 tools/dp_check.py > gpurun_out/r2_fin_dpd_small.log 2>&1; echo "dp_check ddp d=768 multimem rc=$?"; grep -h "world\|mean|dW|\|DP_CHECK\|Error" gpurun_out/r2_fin_dpd_small.log | head -4
+DP_MODE=zero timeout 200 $TR --master-port 29912 tools/dp_trainer_check.py > gpurun_out/r2_fin_ztr.log 2>&1; echo "trainer zero accum=2 rc=$?"; grep -h "checkpoint vs\|after resume\|DP_TRAINER\|Error" gpurun_out/r2_fin_ztr.log | head -5

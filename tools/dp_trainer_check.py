@@ -26,7 +26,7 @@ CFG = dict(n_head=4, n_embed=256, context_length=128, vocab_size=1000)
 L, B, T, LR = 3, 4, 128, 1e-3
 MODE = os.environ.get("DP_MODE", "ddp")
 VP = os.environ.get("DP_VP", "0") == "1"
-ACCUM = 2 if MODE == "ddp" else 1
+ACCUM = 2                                      # gradient accumulation in every mode (sharded: owner-side accumulators)
 STEPS = 3
 
 
