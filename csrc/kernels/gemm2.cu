@@ -47,7 +47,7 @@ __device__ __forceinline__ void st_release_gpu(int* p, int v) {
 
 // AG = true: 4 extra warps (6..9) pull the remote chunks of the layer's weights over NVLink into the local
 // buffer while the tiles whose weights are already local run; the TMA producer waits per chunk.
-template <int BN, bool A_MN, bool B_MN, bool OUT_F32, bool AG>
+template <int BN, bool A_MN, bool B_MN, bool OUT_F32, bool AG, bool COLSUM = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS + 128, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmC, const Params p, const AgParams ag) {
@@ -220,7 +220,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             const int n0_next = (u + npairs < nunits) ? n0_of(u + npairs) : -1;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
             const uint32_t te = ptx::mapa(tempty_bar(acc), 0);   // the leader's accumulator-empty barrier
-            gemm::epilogue_tile<BN, OUT_F32, NG>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base,
+            gemm::epilogue_tile<BN, OUT_F32, NG, COLSUM>(p, &tmC, tfull_bar(acc), acc_phase, taddr, m0, n0, n_blk, row, lane, epi_base,
                                                  buf, store_thread, s_bias, et, bias_pf, n0_next, grp,
                                                  [te]() { ptx::mbar_arrive_cluster(te); });
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -272,10 +272,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool OUT_F32, bool AG = false>
+template <int BN, bool A_MN, bool B_MN, bool OUT_F32, bool AG = false, bool COLSUM = false>
 int launch2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const Params& p, int grid, cudaStream_t st,
             const AgParams* ag = nullptr) {
-    auto kern = gemm2_kernel<BN, A_MN, B_MN, OUT_F32, AG>;
+    auto kern = gemm2_kernel<BN, A_MN, B_MN, OUT_F32, AG, COLSUM>;
     static bool configured = false;
     if (!configured) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2<BN>::SMEM_BYTES));
@@ -298,11 +298,34 @@ int launch2_major(int a_mn, int b_mn, const CUtensorMap& tA, const CUtensorMap& 
 
 }  // namespace
 
+static int gemm_2cta_impl(const void* A, const void* B, void* Cout, int M, int N, int K, long long lda, long long ldb,
+                          long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias,
+                          int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out,
+                          const void* relu_bits, int bn, int split_k, float* colsum, cudaStream_t st);
+
 // Same contract as b200_gemm, tiles of 256 x bn (bn = 256 or 128) on CTA pairs.
 extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, int N, int K, long long lda, long long ldb,
                               long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias,
                               int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out,
                          const void* relu_bits, int bn, int split_k, cudaStream_t st) {
+    return gemm_2cta_impl(A, B, Cout, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_f32, f32_mode, alpha, bias, relu, mask, ld_mask,
+                          stats, relu_bits_out, relu_bits, bn, split_k, nullptr, st);
+}
+
+// Same, and colsum[N] (fp32, must hold the running sum - zero it for a fresh one) += the column sums of the bf16 output:
+// the bias gradient of the Linear whose output gradient this dgrad GEMM produces, without a second pass over it.
+extern "C" int b200_gemm_2cta_colsum(const void* A, const void* B, void* Cout, int M, int N, int K, long long lda,
+                                     long long ldb, long long ldc, int a_mn, int b_mn, float alpha, const float* bias, int relu,
+                                     void* relu_bits_out, const void* relu_bits, int bn, float* colsum, cudaStream_t st) {
+    B200_REQUIRE(colsum != nullptr, "gemm_2cta_colsum: colsum is null");
+    return gemm_2cta_impl(A, B, Cout, M, N, K, lda, ldb, ldc, a_mn, b_mn, 0, 0, alpha, bias, relu, nullptr, 0, nullptr,
+                          relu_bits_out, relu_bits, bn, 1, colsum, st);
+}
+
+static int gemm_2cta_impl(const void* A, const void* B, void* Cout, int M, int N, int K, long long lda, long long ldb,
+                          long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias,
+                          int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out,
+                          const void* relu_bits, int bn, int split_k, float* colsum, cudaStream_t st) {
     B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_2cta: empty problem");
     B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_2cta: lda/ldb must be multiples of 8 elements");
     B200_REQUIRE(out_f32 ? (ldc % 4 == 0 && N % 4 == 0) : (ldc % 8 == 0), "gemm_2cta: bad ldc / N alignment");
@@ -330,6 +353,7 @@ extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, i
     p.bias = bias; p.relu = relu; p.mask = (const bf16*)mask; p.ld_mask = ld_mask; p.stats = (float2*)stats;
     p.relu_bits_out = (unsigned long long*)relu_bits_out; p.relu_bits = (const unsigned long long*)relu_bits;
     p.out_f32 = (float*)Cout; p.ldc = ldc; p.f32_mode = f32_mode;
+    p.colsum = colsum;
 
     CUtensorMap tA, tB, tC;
     memset(&tC, 0, sizeof(tC));
@@ -342,6 +366,13 @@ extern "C" int b200_gemm_2cta(const void* A, const void* B, void* Cout, int M, i
     const int nunits = p.num_m * p.num_n * p.splits;
     const int grid = 2 * min(nunits, sms / 2);
     int rc;
+    if (colsum != nullptr) {
+        // the fused column sums exist for the one shape that needs them: a bf16 dgrad (A K-major, B MN-major), 256-wide tiles
+        B200_REQUIRE(!out_f32 && !a_mn && b_mn && BN == 256, "gemm_2cta_colsum: only the bf16 dgrad form (A K-major, B [K,N], bn 256)");
+        rc = launch2<256, false, true, false, false, true>(tA, tB, tC, p, grid, st);
+        if (rc) return rc;
+        B200_RETURN_LAUNCH_STATUS("gemm_2cta_colsum");
+    }
     if (out_f32) rc = BN == 256 ? launch2_major<256, true>(a_mn, b_mn, tA, tB, tC, p, grid, st)
                                 : launch2_major<128, true>(a_mn, b_mn, tA, tB, tC, p, grid, st);
     else         rc = BN == 256 ? launch2_major<256, false>(a_mn, b_mn, tA, tB, tC, p, grid, st)

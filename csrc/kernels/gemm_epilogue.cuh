@@ -36,6 +36,8 @@ struct Params {
     long long ldc;
     int f32_mode;           // 0 store, 1 accumulate (+=), 2 atomic add
     int n_shift;            // rotate the n-tile order (all-gather fused GEMM: start with the locally owned rows)
+    float* colsum;          // [N] fp32 or null: += column sums of the bf16 outputs (bias gradient of the producing Linear),
+                            // summed from the staged smem tile, one fp32 atomic per column and 128-row tile
 };
 
 // All-gather fused into the GEMM (sharded data parallelism): the B operand (a weight matrix) lives in a flat
@@ -67,7 +69,7 @@ struct AgParams {
 // thread's lane quarter at the accumulator stage's first column; m0: first global row of this CTA's 128 rows.
 // bias_pf: this thread's share of the CURRENT tile's bias slice, loaded one tile ahead (n0_next: first column of the
 // next tile of this CTA, < 0 if none) so the global-load latency never sits in front of a tile's epilogue.
-template <int BN, bool OUT_F32, int NG, class ArriveFn>
+template <int BN, bool OUT_F32, int NG, bool COLSUM = false, class ArriveFn>
 __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap* tmC, uint32_t tfull_bar, uint32_t acc_phase,
                                               uint32_t taddr, int m0, int n0, int n_blk, int row, int lane,
                                               uint32_t epi_base, int& buf, bool store_thread, float* s_bias, int et,
@@ -283,6 +285,25 @@ __device__ __forceinline__ void epilogue_tile(const Params& p, const CUtensorMap
             if (store_thread) {
                 if (nc0 < p.N) ptx::tma_store_2d(tmC, epi_base + buf * EPI_BUF_BYTES, nc0, m0);
                 ptx::tma_store_commit();
+            }
+            if (COLSUM) {
+                // Column sums of the staged 128 x 64 bf16 chunk (the values the consumer will read): thread t sums column
+                // t % 64 over rows [64 * (t / 64), +64) of the swizzled tile - the 32 lanes of a warp read 64 consecutive
+                // bytes of one row per step (conflict-free) - and adds its half to colsum[n] with one fp32 atomic.  The
+                // buffer is not overwritten before the next chunk's barrier, which every thread passes after these reads.
+                const int tg = et - 128 * grp;               // 0..127 inside this epilogue group
+                const int cj = tg & 63, r_lo = (tg >> 6) * 64;
+                const uint32_t cbase = epi_base + buf * EPI_BUF_BYTES + (uint32_t)((cj & 7) * 2);
+                float cs = 0.f;
+#pragma unroll 4
+                for (int rr = 0; rr < 64; ++rr) {
+                    const int rw = r_lo + rr;
+                    const uint32_t addr = cbase + (uint32_t)rw * 128u + ((((uint32_t)cj >> 3) ^ ((uint32_t)rw & 7u)) << 4);
+                    unsigned short hv;
+                    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hv) : "r"(addr));
+                    if (m0 + rw < p.M) cs += __bfloat162float(__ushort_as_bfloat16(hv));
+                }
+                if (nc0 + cj < p.N) atomicAdd(p.colsum + nc0 + cj, cs);
             }
             if (NG == 1) buf ^= 1;
         }

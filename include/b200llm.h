@@ -88,6 +88,11 @@ int b200_gemm(const void* A, const void* B, void* C, int M, int N, int K, long l
  * stages half of the operands, 6-8 pipeline stages.  The default for large problems. */
 int b200_gemm_2cta(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, int out_f32, int f32_mode, float alpha, const float* bias, int relu, const void* mask, int ld_mask, void* stats, void* relu_bits_out, const void* relu_bits, int bn, int split_k, cudaStream_t st);
 
+/* bf16-output form of b200_gemm_2cta that also accumulates colsum[N] (fp32) += column sums of the output - the bias
+ * gradient of the Linear whose output gradient this dgrad GEMM produces (ref: autograd of nn.Linear bias, mlp.py:53),
+ * summed from the staged smem tile instead of by a second pass over the output.  Zero colsum for a fresh sum. */
+int b200_gemm_2cta_colsum(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb, long long ldc, int a_mn, int b_mn, float alpha, const float* bias, int relu, void* relu_bits_out, const void* relu_bits, int bn, float* colsum, cudaStream_t st);
+
 /* All-gather fused into a GEMM (sharded data parallelism; absent in the reference - SURVEY N6/T11).
  * C[M,N] = A[M,K] * opB^T (+bias) (ReLU -> relu_bits_out | masked by relu_bits), bf16 out; Bw points into a LOCAL
  * window of gathered layer weights (b_mn = 0: [N,K]; 1: [K,N]).  The launch carries njobs (0..2) gather jobs: extra

@@ -51,14 +51,17 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
          bias: Optional[torch.Tensor] = None, relu: bool = False, mask: Optional[torch.Tensor] = None,
          stats: Optional[torch.Tensor] = None, bn: int = 0, split_k: int = 0,
          two_cta: Optional[bool] = None, relu_bits_out: Optional[torch.Tensor] = None,
-         relu_bits: Optional[torch.Tensor] = None) -> torch.Tensor:
+         relu_bits: Optional[torch.Tensor] = None, colsum_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """C[M,N] = alpha * opA @ opB^T on the tcgen05 kernel.
 
     a: [M,K] (a_mn=False) or [K,M] (a_mn=True); b: [N,K] (b_mn=False) or [K,N] (b_mn=True); bf16,
     last dim contiguous.  out bf16 (epilogue: +bias, ReLU, *(mask>0), softmax stats) or fp32
     (f32_mode 0 store / 1 accumulate / 2 atomic+split-K).
     relu_bits_out / relu_bits: int64 [M, ceil(N/64)] sign bits of the ReLU output, written by the forward GEMM and
-    applied by the matching dgrad GEMM (the fast replacement of mask=activations)."""
+    applied by the matching dgrad GEMM (the fast replacement of mask=activations).
+    colsum_out: fp32 [N] that receives += the column sums of the bf16 output (the bias gradient of the Linear whose output
+    gradient a dgrad GEMM produces).  Fused into the epilogue of the CTA-pair kernel for the dgrad form (a K-major, b_mn,
+    bf16 out); any other form falls back to the separate column-sum kernel."""
     assert a.dtype == BF16 and b.dtype == BF16 and a.stride(-1) == 1 and b.stride(-1) == 1
     if a_mn:
         K, M = a.shape
@@ -85,6 +88,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
     L = lib.load()
     if two_cta is None:
         two_cta = GEMM_2CTA and M >= 512 and N >= 256 and bn in (0, 128, 256)
+    if colsum_out is not None:
+        assert colsum_out.dtype == F32 and colsum_out.is_contiguous() and colsum_out.numel() == N and not out_f32
+        fused = (two_cta and not a_mn and b_mn and bn in (0, 256) and mask is None and stats is None and FUSED_COLSUM)
+        if fused:
+            rc = L.b200_gemm_2cta_colsum(_p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0), 0, 1,
+                                         float(alpha), _p(bias), int(relu), _p(relu_bits_out), _p(relu_bits), 256,
+                                         _p(colsum_out), _st())
+            _chk(rc, "gemm")
+            return out
     fn = L.b200_gemm_2cta if two_cta else L.b200_gemm
     if two_cta and bn == 0:
         bn = 256
@@ -100,7 +112,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *
             _p(mask), 0 if mask is None else mask.stride(0), _p(stats), _p(relu_bits_out), _p(relu_bits), bn, split_k,
             _st())
     _chk(rc, "gemm")
+    if colsum_out is not None:
+        colsum(out, out=colsum_out, accumulate=True)
     return out
+
+
+FUSED_COLSUM = os.environ.get("B200_FUSED_COLSUM", "1") == "1"
 
 
 def gemm_stats_entries(N: int, bn: int = 256) -> int:

@@ -322,10 +322,18 @@ class Engine:
                 z.before_layer_bwd(l)          # the gradient window of layer l+2 must have been reduced by every rank
             # ---- MLP
             on_w(lambda: ops.gemm(dxa, w.act[l], out=self.G(pre + "mlp.proj.weight"), a_mn=True, b_mn=True, f32_mode=fm))
-            ops.gemm(dxa, self.W(pre + "mlp.proj.weight"), out=dh, b_mn=True, relu_bits=w.relu_bits[l])
+            fused_bias = not DETERMINISTIC        # bias gradient of the MLP-up Linear: column sums of dh, taken from the
+            if fused_bias:                         # dgrad GEMM's staged tiles (fp32 atomics) instead of a second pass
+                if not accumulate:
+                    ops.zero_(self.G(pre + "mlp.hidden.bias"))
+                ops.gemm(dxa, self.W(pre + "mlp.proj.weight"), out=dh, b_mn=True, relu_bits=w.relu_bits[l],
+                         colsum_out=self.G(pre + "mlp.hidden.bias"))
+            else:
+                ops.gemm(dxa, self.W(pre + "mlp.proj.weight"), out=dh, b_mn=True, relu_bits=w.relu_bits[l])
 
             def mlp_up_wgrad():
-                ops.colsum(dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
+                if not fused_bias:
+                    ops.colsum(dh, out=self.G(pre + "mlp.hidden.bias"), accumulate=accumulate)
                 ops.gemm(dh, w.h2[l], out=self.G(pre + "mlp.hidden.weight"), a_mn=True, b_mn=True, f32_mode=fm)
             on_w(mlp_up_wgrad)
             if z is not None:                  # carries the all-gather of layer l-1's weights for its backward

@@ -400,3 +400,22 @@ def test_forward_embedding_runs_on_the_native_kernels():
     n1 = _ops.LAUNCHES
     hid_g, _ = m.forward_embedding(x)                           # grad mode: PyTorch path, differentiable
     assert _ops.LAUNCHES == n1 and hid_g.requires_grad
+
+
+@pytest.mark.parametrize("shape", [(1024, 3072, 768), (1000, 712, 328), (16384, 3072, 768)])
+def test_gemm_dgrad_with_fused_column_sums(ops, shape):
+    """dgrad GEMM (A K-major, B [K, N]) whose epilogue also accumulates the column sums of its bf16 output (the bias
+    gradient), with the ReLU sign-bit mask, against torch: the GEMM result, a fresh sum and an accumulated one."""
+    torch.manual_seed(13)
+    M, N, K = shape
+    a, b = _rand(M, K), _rand(K, N, scale=0.1)
+    bits = torch.randint(-2 ** 62, 2 ** 62, (M, (N + 63) // 64), device="cuda", dtype=torch.int64)
+    keep = ((bits.unsqueeze(-1) >> torch.arange(64, device="cuda")) & 1).bool().view(M, -1)[:, :N]
+    ref = (a.float() @ b.float()) * keep
+    cs = torch.zeros(N, device="cuda")
+    out = ops.gemm(a, b, b_mn=True, relu_bits=bits, colsum_out=cs, two_cta=True)
+    assert _rel(out, ref) < 6e-3
+    want = out.float().sum(0)
+    assert _rel(cs, want) < 1e-4, _rel(cs, want)
+    ops.gemm(a, b, out=out, b_mn=True, relu_bits=bits, colsum_out=cs, two_cta=True)       # accumulates
+    assert _rel(cs, 2 * want) < 1e-4
