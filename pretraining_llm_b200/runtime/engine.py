@@ -25,7 +25,6 @@ sums).  See DESIGN.md for the buffer plan.
 """
 from __future__ import annotations
 
-import math
 import os
 from typing import Dict, Optional, Tuple
 

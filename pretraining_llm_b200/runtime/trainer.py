@@ -12,7 +12,6 @@ on CPU it is plain PyTorch with ``torch.optim.AdamW`` - same numbers, same check
 from __future__ import annotations
 
 import json
-import math
 import os
 import time
 from typing import Iterator, Optional
